@@ -1,0 +1,198 @@
+"""ctypes binding of the CPU oracle (oracle/frodo_oracle.c).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs.  The product package never
+imports this module.  All arrays are numpy, C-contiguous.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libfrodo_oracle.so")
+_lib = None
+
+_c_i = ctypes.c_int
+_c_f = ctypes.c_float
+_c_p = ctypes.c_void_p
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "frodo_oracle.c")
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-B", "libfrodo_oracle.so"],
+                              stdout=subprocess.DEVNULL)
+    return _LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            build()
+        _lib = ctypes.CDLL(_LIB_PATH)
+        _lib.oracle_num_threads.restype = _c_i
+        _lib.oracle_edge_index.restype = _c_i
+        _lib.oracle_chol_solve.restype = _c_i
+        _lib.oracle_gauss_newton.restype = _c_i
+    return _lib
+
+
+def _p(a):
+    return None if a is None else ctypes.c_void_p(a.ctypes.data)
+
+
+def _c(a, dtype):
+    a = np.ascontiguousarray(a, dtype=dtype)
+    return a
+
+
+def num_threads():
+    return lib().oracle_num_threads()
+
+
+def set_num_threads(n):
+    lib().oracle_set_num_threads(_c_i(n))
+
+
+def iter_proj(rays, pts, p_init, max_iter, lambda_init, cost_thresh):
+    """matching_kernels.cu:128-284.  Returns (p_new f32 [B,N,2], converged bool [B,N])."""
+    rays = _c(rays, np.float32)
+    pts = _c(pts, np.float32)
+    p_init = _c(p_init, np.float32)
+    B, H, W, C = rays.shape
+    assert C == 9
+    N = p_init.shape[1]
+    p_new = np.zeros((B, N, 2), np.float32)
+    conv = np.zeros((B, N), np.uint8)
+    lib().oracle_iter_proj(_p(rays), _p(pts), _p(p_init), _p(p_new), _p(conv), _c_i(B), _c_i(H),
+                           _c_i(W), _c_i(N), _c_i(max_iter), _c_f(lambda_init), _c_f(cost_thresh))
+    return p_new, conv.astype(bool)
+
+
+def refine_matches(D11, D21, p1, radius, dilation_max):
+    """matching_kernels.cu:25-85.  D11/D21 float16 or float32.  Returns (p1_new i64, scores)."""
+    p1 = _c(p1, np.int64)
+    B, H, W, F = D11.shape
+    N = p1.shape[1]
+    p1_new = np.zeros((B, N, 2), np.int64)
+    if D11.dtype == np.float16:
+        D11 = _c(D11, np.float16)
+        D21 = _c(D21, np.float16)
+        scores = np.zeros((B, N), np.float16)
+        fn = lib().oracle_refine_matches_f16
+    elif D11.dtype == np.float32:
+        D11 = _c(D11, np.float32)
+        D21 = _c(D21, np.float32)
+        scores = np.zeros((B, N), np.float32)
+        fn = lib().oracle_refine_matches_f32
+    else:
+        raise TypeError(D11.dtype)
+    fn(_p(D11), _p(D21), _p(p1), _p(p1_new), _p(scores), _c_i(B), _c_i(H), _c_i(W), _c_i(N),
+       _c_i(F), _c_i(radius), _c_i(dilation_max))
+    return p1_new, scores
+
+
+def edge_index(ii, jj):
+    """get_unique_kf_idx + create_inds(pin=0), gn_kernels.cu:203-212."""
+    ii = _c(ii, np.int64)
+    jj = _c(jj, np.int64)
+    E = ii.shape[0]
+    ie = np.zeros(E, np.int64)
+    je = np.zeros(E, np.int64)
+    nu = lib().oracle_edge_index(_p(ii), _p(jj), _c_i(E), _p(ie), _p(je))
+    return ie, je, nu
+
+
+MODES = {"rays": 0, "points": 1, "calib": 2}
+
+
+def edge_blocks(mode, Twc, Xs, Cs, ii_edge, jj_edge, idx, valid, Q, sigma_a, sigma_b, C_thresh,
+                Q_thresh, K=None, height=0, width=0, pixel_border=0, z_eps=0.0):
+    """Per-edge Hs [4,E,7,7], gs [2,E,7] in fp64 (reference layout, gn_kernels.cu:865-906)."""
+    Twc = _c(Twc, np.float32).reshape(-1, 8)
+    Xs = _c(Xs, np.float32)
+    Cs = _c(Cs, np.float32)
+    nK, N = Xs.shape[0], Xs.shape[1]
+    ii_edge = _c(ii_edge, np.int64)
+    jj_edge = _c(jj_edge, np.int64)
+    E = ii_edge.shape[0]
+    idx = _c(idx, np.int64).reshape(E, N)
+    valid = _c(np.asarray(valid).reshape(E, N), np.uint8)
+    Q = _c(Q, np.float32).reshape(E, N)
+    Kc = None if K is None else _c(K, np.float32)
+    Hs = np.zeros((4, E, 7, 7), np.float64)
+    gs = np.zeros((2, E, 7), np.float64)
+    lib().oracle_edge_blocks(_c_i(MODES[mode]), _p(Twc), _p(Xs), _p(Cs), _p(Kc), _p(ii_edge),
+                             _p(jj_edge), _p(idx), _p(valid), _p(Q), _c_i(nK), _c_i(N), _c_i(E),
+                             _c_i(height), _c_i(width), _c_i(pixel_border), _c_f(z_eps),
+                             _c_f(sigma_a), _c_f(sigma_b), _c_f(C_thresh), _c_f(Q_thresh), _p(Hs),
+                             _p(gs))
+    return Hs, gs
+
+
+def assemble(Hs, gs, ii_edge, jj_edge, num_kf, num_fix, round_f32=True):
+    Hs = _c(Hs, np.float64)
+    gs = _c(gs, np.float64)
+    ii_edge = _c(ii_edge, np.int64)
+    jj_edge = _c(jj_edge, np.int64)
+    E = ii_edge.shape[0]
+    n = 7 * (num_kf - num_fix)
+    H = np.zeros((n, n), np.float64)
+    g = np.zeros(n, np.float64)
+    lib().oracle_assemble(_p(Hs), _p(gs), _p(ii_edge), _p(jj_edge), _c_i(E), _c_i(num_kf),
+                          _c_i(num_fix), _c_i(1 if round_f32 else 0), _p(H), _p(g))
+    return H, g
+
+
+def chol_solve(H, g):
+    H = _c(H, np.float64)
+    g = _c(g, np.float64)
+    n = g.shape[0]
+    x = np.zeros(n, np.float64)
+    fail = lib().oracle_chol_solve(_p(H), _p(g), _c_i(n), _p(x))
+    return x, bool(fail)
+
+
+def pose_retr(Twc, dx, num_fix):
+    Twc = np.array(Twc, dtype=np.float32, copy=True).reshape(-1, 8)
+    dx = _c(dx, np.float32)
+    lib().oracle_pose_retr(_p(Twc), _p(dx), _c_i(Twc.shape[0]), _c_i(num_fix))
+    return Twc
+
+
+def gauss_newton(mode, Twc, Xs, Cs, ii, jj, idx, valid, Q, sigma_a, sigma_b, C_thresh, Q_thresh,
+                 num_fix, max_iter, delta_thresh, K=None, height=0, width=0, pixel_border=0,
+                 z_eps=0.0, return_system=False):
+    """gauss_newton_{rays,points,calib}_cuda (gn_kernels.cu:909-995, 2206-2293, 2610-2702).
+
+    Returns dict(Twc=updated copy, dx=[K-num_fix,7], iters=int, fails=int[, H, g of iter 0]).
+    """
+    Twc = np.array(Twc, dtype=np.float32, copy=True).reshape(-1, 8)
+    Xs = _c(Xs, np.float32)
+    Cs = _c(Cs, np.float32)
+    nK, N = Xs.shape[0], Xs.shape[1]
+    ii = _c(ii, np.int64)
+    jj = _c(jj, np.int64)
+    E = ii.shape[0]
+    idx = _c(idx, np.int64).reshape(E, N)
+    valid = _c(np.asarray(valid).reshape(E, N), np.uint8)
+    Q = _c(Q, np.float32).reshape(E, N)
+    Kc = None if K is None else _c(K, np.float32)
+    n = 7 * (nK - num_fix)
+    dx = np.zeros((nK - num_fix, 7), np.float32)
+    H = np.zeros((n, n), np.float64) if return_system else None
+    g = np.zeros(n, np.float64) if return_system else None
+    fails = ctypes.c_int(0)
+    iters = lib().oracle_gauss_newton(
+        _c_i(MODES[mode]), _p(Twc), _p(Xs), _p(Cs), _p(Kc), _p(ii), _p(jj), _p(idx), _p(valid),
+        _p(Q), _c_i(nK), _c_i(N), _c_i(E), _c_i(height), _c_i(width), _c_i(pixel_border),
+        _c_f(z_eps), _c_f(sigma_a), _c_f(sigma_b), _c_f(C_thresh), _c_f(Q_thresh), _c_i(num_fix),
+        _c_i(max_iter), _c_f(delta_thresh), _p(dx), _p(H), _p(g), ctypes.byref(fails))
+    out = dict(Twc=Twc, dx=dx, iters=iters, fails=fails.value)
+    if return_system:
+        out["H"] = H
+        out["g"] = g
+    return out
