@@ -1,0 +1,70 @@
+"""ctypes loader for libfrodo_b200.so (the C ABI declared in include/frodo_b200.h).
+
+The library is the only compute path of this package: if it is missing or fails
+to load, importing the operators raises -- there is no CPU or PyTorch fallback.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libfrodo_b200.so")
+
+c_int, c_float, c_void_p, c_size_t = ctypes.c_int, ctypes.c_float, ctypes.c_void_p, ctypes.c_size_t
+
+
+class GnParams(ctypes.Structure):
+    """struct frodo_gn_params (include/frodo_b200.h)."""
+    _fields_ = [("mode", c_int), ("sigma_a", c_float), ("sigma_b", c_float),
+                ("C_thresh", c_float), ("Q_thresh", c_float), ("height", c_int),
+                ("width", c_int), ("pixel_border", c_int), ("z_eps", c_float)]
+
+
+GN_RAYS, GN_POINTS, GN_CALIB = 0, 1, 2
+
+# name -> (restype, argtypes); kept in sync with include/frodo_b200.h (tests check this)
+SIGNATURES = {
+    "frodo_version": (c_int, []),
+    "frodo_last_error": (ctypes.c_char_p, []),
+    "frodo_iter_proj": (c_int, [c_void_p] * 5 + [c_int] * 5 + [c_float, c_float, c_void_p]),
+    "frodo_refine_matches_f16": (c_int, [c_void_p] * 5 + [c_int] * 7 + [c_void_p]),
+    "frodo_refine_matches_f32": (c_int, [c_void_p] * 5 + [c_int] * 7 + [c_void_p]),
+    "frodo_gn_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "frodo_gn_workspace_init": (c_int, [c_void_p, c_size_t, c_int, c_int, c_int, c_void_p]),
+    "frodo_gn_edge_index": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
+                                    c_void_p]),
+    "frodo_gn_accumulate": (c_int, [ctypes.POINTER(GnParams)] + [c_void_p] * 9 + [c_int] * 4 +
+                            [c_void_p] * 4 + [c_size_t, c_void_p]),
+    "frodo_gn_solve_retract": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float,
+                                       c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "frodo_gauss_newton": (c_int, [ctypes.POINTER(GnParams)] + [c_void_p] * 9 + [c_int] * 5 +
+                           [c_float, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+}
+
+_lib = None
+
+
+class FrodoError(RuntimeError):
+    pass
+
+
+def load():
+    """Load the CUDA library (once).  Raises FrodoError if it is not built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FrodoError(
+                f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; "
+                "g.build()'` (nvcc, sm_100a). There is no CPU fallback.")
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        msg = load().frodo_last_error().decode("utf-8", "replace")
+        raise FrodoError(f"libfrodo_b200 error {rc}: {msg}")

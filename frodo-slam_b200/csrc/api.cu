@@ -1,0 +1,183 @@
+// C ABI of libfrodo_b200.so (see include/frodo_b200.h).
+#include <stdarg.h>
+#include <string.h>
+
+#include "gn_internal.cuh"
+
+namespace frodo {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+  return FRODO_ERR_CUDA;
+}
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+size_t gn_carve_workspace(void* base, int K, int E, int N, GnWorkspace* ws) {
+  const size_t Ez = (size_t)(E > 0 ? E : 1);
+  const size_t n = (size_t)7 * (size_t)(K > 0 ? K : 1);
+  const size_t max_chunks = ((size_t)(N > 0 ? N : 1) + 1023) / 1024;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off = align_up(off + bytes, 256);
+    return o;
+  };
+  const size_t o_ii = take(Ez * sizeof(int32_t));
+  const size_t o_jj = take(Ez * sizeof(int32_t));
+  const size_t o_sc = take(8 * sizeof(int32_t));
+  const size_t o_tk = take(Ez * sizeof(int32_t));
+  const size_t o_pt = take(Ez * max_chunks * kGnBlock * sizeof(float));
+  const size_t o_eb = take(Ez * kGnBlock * sizeof(double));
+  const size_t o_hg = take((n + 1) * n * sizeof(double));
+  if (base != nullptr && ws != nullptr) {
+    char* b = static_cast<char*>(base);
+    ws->ii_row = reinterpret_cast<int32_t*>(b + o_ii);
+    ws->jj_row = reinterpret_cast<int32_t*>(b + o_jj);
+    ws->scalars = reinterpret_cast<int32_t*>(b + o_sc);
+    ws->tickets = reinterpret_cast<int32_t*>(b + o_tk);
+    ws->partials = reinterpret_cast<float*>(b + o_pt);
+    ws->edge_blocks = reinterpret_cast<double*>(b + o_eb);
+    ws->Hg = reinterpret_cast<double*>(b + o_hg);
+    ws->bytes = off;
+  }
+  return off;
+}
+
+}  // namespace frodo
+
+using namespace frodo;
+
+extern "C" {
+
+int frodo_version(void) { return 100; }
+
+const char* frodo_last_error(void) { return g_err; }
+
+int frodo_iter_proj(const float* rays_img, const float* pts_3d_norm, const float* p_init,
+                    float* p_new, uint8_t* converged, int B, int H, int W, int N, int max_iter,
+                    float lambda_init, float cost_thresh, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(B >= 0 && B <= 65535 && N >= 0 && H >= 3 && W >= 3);
+  FRODO_ARG_CHECK(B == 0 || N == 0 ||
+                  (rays_img && pts_3d_norm && p_init && p_new && converged));
+  return launch_iter_proj(rays_img, pts_3d_norm, p_init, p_new, converged, B, H, W, N, max_iter,
+                          lambda_init, cost_thresh, static_cast<cudaStream_t>(stream));
+}
+
+int frodo_refine_matches_f16(const void* D11, const void* D21, const int64_t* p1, int64_t* p1_new,
+                             void* max_scores, int B, int H, int W, int N, int F, int radius,
+                             int dilation_max, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(B >= 0 && B <= 65535 && N >= 0 && H >= 1 && W >= 1 && F >= 1 && radius >= 0);
+  FRODO_ARG_CHECK(B == 0 || N == 0 || (D11 && D21 && p1 && p1_new && max_scores));
+  return launch_refine_f16(static_cast<const __half*>(D11), static_cast<const __half*>(D21), p1,
+                           p1_new, static_cast<__half*>(max_scores), B, H, W, N, F, radius,
+                           dilation_max, static_cast<cudaStream_t>(stream));
+}
+
+int frodo_refine_matches_f32(const float* D11, const float* D21, const int64_t* p1,
+                             int64_t* p1_new, float* max_scores, int B, int H, int W, int N, int F,
+                             int radius, int dilation_max, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(B >= 0 && B <= 65535 && N >= 0 && H >= 1 && W >= 1 && F >= 1 && radius >= 0);
+  FRODO_ARG_CHECK(B == 0 || N == 0 || (D11 && D21 && p1 && p1_new && max_scores));
+  return launch_refine_f32(D11, D21, p1, p1_new, max_scores, B, H, W, N, F, radius, dilation_max,
+                           static_cast<cudaStream_t>(stream));
+}
+
+size_t frodo_gn_workspace_bytes(int K, int E, int N) {
+  return gn_carve_workspace(nullptr, K, E, N, nullptr);
+}
+
+int frodo_gn_edge_index(const int64_t* ii, const int64_t* jj, int E, int32_t* ii_row,
+                        int32_t* jj_row, int32_t* n_unique, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(E >= 0);
+  FRODO_ARG_CHECK(E == 0 || (ii && jj && ii_row && jj_row));
+  return launch_gn_edge_index(ii, jj, E, ii_row, jj_row, n_unique,
+                              static_cast<cudaStream_t>(stream));
+}
+
+int frodo_gn_accumulate(const frodo_gn_params* params, const float* Twc, const float* Xs,
+                        const float* Cs, const float* Kmat, const int32_t* ii_row,
+                        const int32_t* jj_row, const int64_t* idx_ii2jj,
+                        const uint8_t* valid_match, const float* Q, int K, int N, int E,
+                        int num_fix, double* Hg, double* edge_blocks, const int32_t* done,
+                        void* workspace, size_t workspace_bytes, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(params != nullptr && K >= 1 && N >= 0 && E >= 0 && num_fix >= 0);
+  FRODO_ARG_CHECK(params->mode != FRODO_GN_CALIB || Kmat != nullptr);
+  FRODO_ARG_CHECK(E <= 65535);
+  FRODO_ARG_CHECK(Hg != nullptr && workspace != nullptr);
+  FRODO_ARG_CHECK(workspace_bytes >= gn_carve_workspace(nullptr, K, E, N, nullptr));
+  FRODO_ARG_CHECK(E == 0 || (Twc && Xs && Cs && ii_row && jj_row && idx_ii2jj && valid_match && Q));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  GnWorkspace ws;
+  gn_carve_workspace(workspace, K, E, N, &ws);
+  double* eb = edge_blocks ? edge_blocks : ws.edge_blocks;
+  int rc = launch_gn_accumulate(*params, Twc, Xs, Cs, Kmat, ii_row, jj_row, idx_ii2jj,
+                                valid_match, Q, N, E, ws.partials, ws.tickets, eb, done, s);
+  if (rc) return rc;
+  return launch_gn_assemble(eb, ii_row, jj_row, E, K, num_fix, Hg, done, s);
+}
+
+int frodo_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fix,
+                           float delta_thresh, int32_t* done, int32_t* info, void* workspace,
+                           size_t workspace_bytes, frodo_stream_t stream) {
+  (void)workspace;
+  (void)workspace_bytes;
+  FRODO_ARG_CHECK(K >= 1 && num_fix >= 0 && num_fix <= K);
+  FRODO_ARG_CHECK(K == num_fix || (Hg && Twc && dx));
+  return launch_gn_solve_retract(Hg, Twc, dx, K, num_fix, delta_thresh, done, info,
+                                 static_cast<cudaStream_t>(stream));
+}
+
+int frodo_gn_workspace_init(void* workspace, size_t workspace_bytes, int K, int E, int N,
+                            frodo_stream_t stream) {
+  FRODO_ARG_CHECK(workspace != nullptr);
+  FRODO_ARG_CHECK(workspace_bytes >= gn_carve_workspace(nullptr, K, E, N, nullptr));
+  GnWorkspace ws;
+  gn_carve_workspace(workspace, K, E, N, &ws);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  FRODO_CUDA_TRY(cudaMemsetAsync(ws.scalars, 0, 8 * sizeof(int32_t), s));
+  FRODO_CUDA_TRY(cudaMemsetAsync(ws.tickets, 0, (size_t)(E > 0 ? E : 1) * sizeof(int32_t), s));
+  return FRODO_OK;
+}
+
+int frodo_gauss_newton(const frodo_gn_params* params, float* Twc, const float* Xs, const float* Cs,
+                       const float* Kmat, const int64_t* ii, const int64_t* jj,
+                       const int64_t* idx_ii2jj, const uint8_t* valid_match, const float* Q, int K,
+                       int N, int E, int num_fix, int max_iter, float delta_thresh, float* dx,
+                       int32_t* info, void* workspace, size_t workspace_bytes,
+                       frodo_stream_t stream) {
+  FRODO_ARG_CHECK(params != nullptr && K >= 1 && N >= 0 && E >= 0 && num_fix >= 0 && num_fix <= K);
+  FRODO_ARG_CHECK(workspace != nullptr);
+  FRODO_ARG_CHECK(workspace_bytes >= gn_carve_workspace(nullptr, K, E, N, nullptr));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  GnWorkspace ws;
+  gn_carve_workspace(workspace, K, E, N, &ws);
+  int rc = frodo_gn_workspace_init(workspace, workspace_bytes, K, E, N, stream);
+  if (rc) return rc;
+  int32_t* done = ws.scalars + 1;
+  int32_t* winfo = ws.scalars + 2;
+  rc = launch_gn_edge_index(ii, jj, E, ws.ii_row, ws.jj_row, ws.scalars, s);
+  if (rc) return rc;
+  for (int it = 0; it < max_iter; ++it) {
+    rc = frodo_gn_accumulate(params, Twc, Xs, Cs, Kmat, ws.ii_row, ws.jj_row, idx_ii2jj,
+                             valid_match, Q, K, N, E, num_fix, ws.Hg, ws.edge_blocks, done,
+                             workspace, workspace_bytes, stream);
+    if (rc) return rc;
+    rc = launch_gn_solve_retract(ws.Hg, Twc, dx, K, num_fix, delta_thresh, done, winfo, s);
+    if (rc) return rc;
+  }
+  if (info != nullptr)
+    FRODO_CUDA_TRY(cudaMemcpyAsync(info, winfo, 2 * sizeof(int32_t), cudaMemcpyDeviceToDevice, s));
+  return FRODO_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,46 @@
+// Shared helpers for libfrodo_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/frodo_b200.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libfrodo_b200 is written for sm_100a (B200) only"
+#endif
+
+namespace frodo {
+
+constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
+
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+
+#define FRODO_CUDA_TRY(expr)                                            \
+  do {                                                                  \
+    cudaError_t _e = (expr);                                            \
+    if (_e != cudaSuccess) return ::frodo::cuda_fail(_e, #expr);        \
+  } while (0)
+
+#define FRODO_ARG_CHECK(cond)                                           \
+  do {                                                                  \
+    if (!(cond)) {                                                      \
+      ::frodo::set_error("invalid argument: %s", #cond);                \
+      return FRODO_ERR_ARG;                                             \
+    }                                                                   \
+  } while (0)
+
+// Launchers implemented in the .cu files (host side, return FRODO_* codes).
+int launch_iter_proj(const float* rays, const float* pts, const float* p_init, float* p_new,
+                     uint8_t* converged, int B, int H, int W, int N, int max_iter,
+                     float lambda_init, float cost_thresh, cudaStream_t s);
+int launch_refine_f16(const __half* D11, const __half* D21, const int64_t* p1, int64_t* p1_new,
+                      __half* scores, int B, int H, int W, int N, int F, int radius, int dil,
+                      cudaStream_t s);
+int launch_refine_f32(const float* D11, const float* D21, const int64_t* p1, int64_t* p1_new,
+                      float* scores, int B, int H, int W, int N, int F, int radius, int dil,
+                      cudaStream_t s);
+
+}  // namespace frodo

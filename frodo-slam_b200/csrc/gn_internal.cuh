@@ -1,0 +1,37 @@
+// Internal declarations shared by the Gauss-Newton translation units.
+#pragma once
+#include "common.cuh"
+
+namespace frodo {
+
+constexpr int kGnBlock = 35;  // per-edge block: 28 upper-tri entries of A + 7 of g_j
+
+// Points handled by one accumulate CTA for a graph of E edges x N points.
+int gn_pts_per_cta(int E, int N);
+
+struct GnWorkspace {
+  int32_t* ii_row;     // [E]
+  int32_t* jj_row;     // [E]
+  int32_t* scalars;    // [8]: 0 n_unique, 1 done, 2..3 info
+  int32_t* tickets;    // [E]  (zero between launches)
+  float* partials;     // [E * nchunks * 35]
+  double* edge_blocks; // [E * 35]
+  double* Hg;          // [(n+1) * n]
+  size_t bytes;
+};
+// Carves `base` (may be NULL to only compute sizes).  Returns total bytes.
+size_t gn_carve_workspace(void* base, int K, int E, int N, GnWorkspace* ws);
+
+int launch_gn_edge_index(const int64_t* ii, const int64_t* jj, int E, int32_t* ii_row,
+                         int32_t* jj_row, int32_t* n_unique, cudaStream_t s);
+int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const float* Xs,
+                         const float* Cs, const float* Kmat, const int32_t* ii_row,
+                         const int32_t* jj_row, const int64_t* idx, const uint8_t* valid,
+                         const float* Q, int N, int E, float* partials, int32_t* tickets,
+                         double* edge_blocks, const int32_t* done, cudaStream_t s);
+int launch_gn_assemble(const double* edge_blocks, const int32_t* ii_row, const int32_t* jj_row,
+                       int E, int K, int num_fix, double* Hg, const int32_t* done, cudaStream_t s);
+int launch_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fix,
+                            float delta_thresh, int32_t* done, int32_t* info, cudaStream_t s);
+
+}  // namespace frodo

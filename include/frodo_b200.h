@@ -1,0 +1,140 @@
+/*
+ * frodo_b200.h -- C ABI of libfrodo_b200.so, the B200 (sm_100a) implementation
+ * of the reference's `mast3r_slam_backends` operator surface.
+ *
+ * Every entry point takes raw DEVICE pointers, plain sizes and scalars, and a
+ * CUDA stream handle (cudaStream_t passed as void*; NULL = legacy default
+ * stream).  All calls are asynchronous with respect to the host unless noted.
+ * Return value: 0 = ok, FRODO_ERR_ARG = bad argument, FRODO_ERR_CUDA = a CUDA
+ * runtime call or launch failed (text via frodo_last_error()).  A failed
+ * Cholesky (system not positive definite) is NOT an error: dx is zero and the
+ * poses are left unchanged, as in the reference (gn_kernels.cu:193-197).
+ *
+ * Reference interfaces replaced (paths relative to the reference repo):
+ *   mast3r_slam/backend/src/gn.cpp:120-135   iter_proj
+ *   mast3r_slam/backend/src/gn.cpp:137-150   refine_matches
+ *   mast3r_slam/backend/src/gn.cpp:63-88     gauss_newton_rays
+ *   mast3r_slam/backend/src/gn.cpp:3-26      gauss_newton_points
+ *   mast3r_slam/backend/src/gn.cpp:90-118    gauss_newton_calib
+ *   mast3r_slam/backend/include/gn.h         (*_cuda launchers)
+ */
+#ifndef FRODO_B200_H
+#define FRODO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FRODO_OK 0
+#define FRODO_ERR_ARG 1
+#define FRODO_ERR_CUDA 2
+
+#define FRODO_GN_RAYS 0
+#define FRODO_GN_POINTS 1
+#define FRODO_GN_CALIB 2
+
+typedef void* frodo_stream_t; /* cudaStream_t */
+
+/* Library version (major*10000 + minor*100 + patch). */
+int frodo_version(void);
+/* Text of the last error on the calling thread ("" if none). */
+const char* frodo_last_error(void);
+
+/* ---- iter_proj: matching_kernels.cu:128-325 -------------------------------
+ * rays_img [B,H,W,9] f32 (ray, d ray/dx, d ray/dy), pts_3d_norm [B,N,3] f32,
+ * p_init [B,N,2] f32 (u,v).  Outputs p_new [B,N,2] f32, converged [B,N] u8
+ * (0/1, layout-compatible with torch.bool).  Bit-exact with the reference
+ * kernel as compiled by nvcc 12.9 -O3 (same FMA contractions). */
+int frodo_iter_proj(const float* rays_img, const float* pts_3d_norm, const float* p_init,
+                    float* p_new, uint8_t* converged, int B, int H, int W, int N, int max_iter,
+                    float lambda_init, float cost_thresh, frodo_stream_t stream);
+
+/* ---- refine_matches: matching_kernels.cu:25-125 ---------------------------
+ * D11 [B,H,W,F], D21 [B,N,F] (IEEE fp16 for _f16, fp32 for _f32), p1 [B,N,2]
+ * i64 (u,v).  Outputs p1_new [B,N,2] i64, max_scores [B,N] (same dtype as D).
+ * fp16 path rounds to fp16 after every multiply and every add (c10::Half). */
+int frodo_refine_matches_f16(const void* D11, const void* D21, const int64_t* p1, int64_t* p1_new,
+                             void* max_scores, int B, int H, int W, int N, int F, int radius,
+                             int dilation_max, frodo_stream_t stream);
+int frodo_refine_matches_f32(const float* D11, const float* D21, const int64_t* p1,
+                             int64_t* p1_new, float* max_scores, int B, int H, int W, int N, int F,
+                             int radius, int dilation_max, frodo_stream_t stream);
+
+/* ---- Gauss-Newton over the keyframe graph ---------------------------------
+ * Shared tensor meanings (gn_kernels.cu:909-995):
+ *   Twc [K,8] f32 = [t(3), q_xyzw(4), s], updated IN PLACE;  Xs [K,N,3] f32;
+ *   Cs [K,N] f32;  ii,jj [E] i64 keyframe ids;  idx_ii2jj [E,N] i64;
+ *   valid_match [E,N] u8;  Q [E,N] f32;  Kmat [3,3] f32 (calib only).
+ * Parameters of the three residual models travel in frodo_gn_params. */
+typedef struct frodo_gn_params {
+  int mode;      /* FRODO_GN_RAYS / POINTS / CALIB                              */
+  float sigma_a; /* rays: sigma_ray   points: sigma_point   calib: sigma_pixel  */
+  float sigma_b; /* rays: sigma_dist  points: unused        calib: sigma_depth  */
+  float C_thresh;
+  float Q_thresh;
+  int height; /* calib only (gn_kernels.cu:2307-2314) */
+  int width;
+  int pixel_border;
+  float z_eps;
+} frodo_gn_params;
+
+/* Bytes of device workspace the GN entry points need for a graph of K
+ * keyframes, E (local) directed edges and N points per keyframe. */
+size_t frodo_gn_workspace_bytes(int K, int E, int N);
+
+/* Zeroes the control words (tickets, convergence flag, counters) of a workspace;
+ * call once before the first frodo_gn_accumulate on a fresh or reused buffer. */
+int frodo_gn_workspace_init(void* workspace, size_t workspace_bytes, int K, int E, int N,
+                            frodo_stream_t stream);
+
+/* get_unique_kf_idx + create_inds (gn_kernels.cu:203-212): writes, for every
+ * edge, the row of its two keyframes among the sorted unique ids of cat(ii,jj)
+ * (ii_row, jj_row: [E] i32) and the number of unique ids (n_unique: [1] i32). */
+int frodo_gn_edge_index(const int64_t* ii, const int64_t* jj, int E, int32_t* ii_row,
+                        int32_t* jj_row, int32_t* n_unique, frodo_stream_t stream);
+
+/* One accumulation pass (ray_align / point_align / calib_proj kernels,
+ * gn_kernels.cu:576-907, 1936-2204, 2295-2607) over the E edges given, followed
+ * by assembly (SparseBlock::update_lhs/rhs, :72-122) into the dense fp64 system
+ *   Hg = [ H (n x n, row-major) | g (n) ],  n = 7*(K - num_fix)
+ * which is OVERWRITTEN (not accumulated into).  Edge rows come from
+ * frodo_gn_edge_index.  edge_blocks (may be NULL) receives per-edge [E,35] f64:
+ * the 28 upper-triangular entries of H_jj (row-major) then g_j; by
+ * construction H_ii = H_jj = -H_ij = -H_ji and g_i = -g_j.
+ * `done` (device int32, may be NULL): when non-zero at kernel time the pass is
+ * skipped (convergence reached, see frodo_gn_solve_retract). */
+int frodo_gn_accumulate(const frodo_gn_params* params, const float* Twc, const float* Xs,
+                        const float* Cs, const float* Kmat, const int32_t* ii_row,
+                        const int32_t* jj_row, const int64_t* idx_ii2jj,
+                        const uint8_t* valid_match, const float* Q, int K, int N, int E,
+                        int num_fix, double* Hg, double* edge_blocks, const int32_t* done,
+                        void* workspace, size_t workspace_bytes, frodo_stream_t stream);
+
+/* dx = -H^{-1} g by dense fp64 Cholesky (SparseBlock::solve, :163-199; zeros on
+ * failure), dx -> f32 [K-num_fix,7]; Twc[k] <- Exp(dx[k-num_fix]) * Twc[k] for
+ * k >= num_fix (pose_retr_kernel :522-560); if ||dx||_2 < delta_thresh sets
+ * *done = 1 (:986-989).  Hg is destroyed.  Skipped when *done != 0 on entry.
+ * info (device int32[2], may be NULL): [0] += 1 per executed iteration,
+ * [1] += 1 per failed factorisation. */
+int frodo_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fix,
+                           float delta_thresh, int32_t* done, int32_t* info, void* workspace,
+                           size_t workspace_bytes, frodo_stream_t stream);
+
+/* Whole single-GPU driver = gauss_newton_{rays,points,calib}_cuda: edge index,
+ * then max_iter x (accumulate, solve_retract) with a device-side convergence
+ * flag; no host synchronisation.  dx [K-num_fix,7] f32 receives the last
+ * executed iteration's update.  info as above (zeroed by this call). */
+int frodo_gauss_newton(const frodo_gn_params* params, float* Twc, const float* Xs, const float* Cs,
+                       const float* Kmat, const int64_t* ii, const int64_t* jj,
+                       const int64_t* idx_ii2jj, const uint8_t* valid_match, const float* Q, int K,
+                       int N, int E, int num_fix, int max_iter, float delta_thresh, float* dx,
+                       int32_t* info, void* workspace, size_t workspace_bytes,
+                       frodo_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FRODO_B200_H */
