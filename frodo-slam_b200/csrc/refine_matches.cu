@@ -33,8 +33,8 @@ __device__ __forceinline__ __half2 score_pair_f16(const __half2* __restrict__ q2
       const __half2 qv = q2[blk * 4 + m];
       const __half2 lo = __lows2half2(av, bv);    // (a_2m,   b_2m)
       const __half2 hi = __highs2half2(av, bv);   // (a_2m+1, b_2m+1)
-      s = __hadd2(s, __hmul2(__low2half2(qv), lo));
-      s = __hadd2(s, __hmul2(__high2half2(qv), hi));
+      s = __hadd2_rn(s, __hmul2_rn(__low2half2(qv), lo));
+      s = __hadd2_rn(s, __hmul2_rn(__high2half2(qv), hi));
     }
   }
   return s;
@@ -128,7 +128,7 @@ refine_f16_generic_kernel(const __half* __restrict__ D11, const __half* __restri
         if (v >= 0 && v < H && u >= 0 && u < W) {
           const __half* row = img + ((size_t)v * W + (size_t)u) * F;
           __half s = __float2half_rn(0.0f);
-          for (int k = 0; k < F; ++k) s = __hadd(s, __hmul(q[k], row[k]));
+          for (int k = 0; k < F; ++k) s = __hadd_rn(s, __hmul_rn(q[k], row[k]));
           if (__hgt(s, max_score)) {
             max_score = s;
             u_new = u;
