@@ -1,0 +1,70 @@
+"""Pins the CPU oracle against golden vectors recorded from the UNMODIFIED reference
+backend on a B200 (tests/golden/make_golden_ref.py -> tests/golden/golden_ref.npz)."""
+import os
+
+import numpy as np
+import pytest
+
+from helpers import GP, MP, rel_err
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "golden_ref.npz")
+
+
+@pytest.fixture(scope="module")
+def gold():
+    assert os.path.exists(GOLD), "golden fixture missing"
+    return np.load(GOLD)
+
+
+def test_iter_proj_oracle_equals_reference_bitwise(gold):
+    from oracle import oracle
+    p, c = oracle.iter_proj(gold["ip_rays"], gold["ip_pts"], gold["ip_p0"], MP["max_iter"],
+                            MP["lambda_init"], MP["convergence_thresh"])
+    assert np.array_equal(p.view(np.uint32), gold["ip_p"].view(np.uint32))
+    assert np.array_equal(c, gold["ip_conv"])
+
+
+def test_refine_f16_oracle_equals_reference_bitwise(gold):
+    from oracle import oracle
+    pn, sc = oracle.refine_matches(gold["rm_D11"], gold["rm_D21"], gold["rm_p1"], MP["radius"],
+                                   MP["dilation_max"])
+    assert np.array_equal(pn, gold["rm_pn"])
+    assert np.array_equal(sc.view(np.uint16), gold["rm_sc"].view(np.uint16))
+
+
+def test_refine_f32_oracle_equals_reference_bitwise(gold):
+    from oracle import oracle
+    pn, sc = oracle.refine_matches(gold["rm_D11"].astype(np.float32),
+                                   gold["rm_D21"].astype(np.float32), gold["rm_p1"], 2, 3)
+    assert np.array_equal(pn, gold["rm32_pn"])
+    assert np.array_equal(sc.view(np.uint32), gold["rm32_sc"].view(np.uint32))
+
+
+def _gn(gold, mode, num_fix, iters):
+    from oracle import oracle
+    H, W = (int(x) for x in gold["gn_HW"])
+    kw = dict(rays=dict(sigma_a=GP["sigma_ray"], sigma_b=GP["sigma_dist"]),
+              points=dict(sigma_a=GP["sigma_point"], sigma_b=0.0),
+              calib=dict(sigma_a=GP["sigma_pixel"], sigma_b=GP["sigma_depth"], K=gold["gn_K"],
+                         height=H, width=W, pixel_border=GP["pixel_border"],
+                         z_eps=GP["depth_eps"]))[mode]
+    return oracle.gauss_newton(mode, gold["gn_Twc"], gold["gn_Xs"], gold["gn_Cs"], gold["gn_ii"],
+                               gold["gn_jj"], gold["gn_idx"].astype(np.int64), gold["gn_valid"],
+                               gold["gn_Q"], C_thresh=GP["C_conf"], Q_thresh=GP["Q_conf"],
+                               num_fix=num_fix, max_iter=iters, delta_thresh=0.0, **kw)
+
+
+@pytest.mark.parametrize("mode", ["rays", "points", "calib"])
+@pytest.mark.parametrize("iters", [1, 3])
+def test_gn_oracle_matches_reference(gold, mode, iters):
+    r = _gn(gold, mode, 1, iters)
+    assert r["fails"] == 0 and r["iters"] == iters
+    assert rel_err(r["Twc"], gold[f"gn_{mode}_{iters}_Twc"]) < 1e-4
+    if iters == 1:
+        assert rel_err(r["dx"], gold[f"gn_{mode}_{iters}_dx"]) < 1e-4
+
+
+def test_gn_oracle_num_fix_2(gold):
+    r = _gn(gold, "rays", 2, 2)
+    assert rel_err(r["Twc"], gold["gn_rays_fix2_Twc"]) < 1e-4
+    assert np.array_equal(r["Twc"][:2], gold["gn_Twc"][:2])  # pinned poses untouched
