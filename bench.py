@@ -1,0 +1,452 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the hot path (BASELINE.json):
+
+  metric   GN-rays iterations/s on the 64-keyframe, 512x384 graph (63 chain + 65 loop
+           closures, both directions -> E = 256 directed edges), edges sharded over N GPUs;
+  matching px-matches/s of iter_proj + refine_matches on B frame pairs at 512x384
+           (reported in the "matching" object of the same JSON line).
+
+A "step" is one gauss_newton_rays call of `--gn-iters` (10, config/base.yaml:56) iterations
+with delta_thresh = 0, i.e. a fixed iteration count.  `value` is timed with every input
+resident in HBM; `e2e` is the same call through the reference-facing operator
+(mast3r_slam_backends.gauss_newton_rays) with HOST (pinned) buffers: H2D of all inputs and
+D2H of the poses inside the timed region.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+For N > 1 launch with torchrun (one rank per GPU).  See the task contract in DESIGN.md.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+H_IMG, W_IMG = 384, 512
+N_PTS = H_IMG * W_IMG
+GN_BYTES_PER_POINT = 45      # 1 + 8 + 12 + 12 + 4 + 4 + 4
+MATCH_BYTES_PER_PX = 195     # 65 (iter_proj) + 130 (refine_matches fp16)
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names)
+                   if any(len(r) >= 6 and r[2 + k].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def build_graph(device, num_kf_cfg="loop64"):
+    from frodo_slam_b200 import synth
+    K, und = synth.graph_edges(num_kf_cfg)
+    g = synth.keyframe_graph(K, H_IMG, W_IMG, und, seed=1, device=device)
+    return K, g
+
+
+def timed_steps(fn, steps, warmup, barrier=None):
+    """W warm-up calls, then K calls bracketed by barrier + synchronize; CUDA-event time (ms)."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if barrier:
+        barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if barrier:
+        barrier()
+    return e0.elapsed_time(e1)
+
+
+def gn_params():
+    from frodo_slam_b200 import backends, synth
+    gp = synth.GN_PARAMS
+    return backends.make_params("rays", sigma_ray=gp["sigma_ray"], sigma_dist=gp["sigma_dist"],
+                                C_thresh=gp["C_conf"], Q_thresh=gp["Q_conf"]), gp
+
+
+def run_matching(device, B, steps, warmup, peak):
+    """px-matches/s of iter_proj + refine_matches over B pairs at 512x384 (inputs in HBM)."""
+    import mast3r_slam_backends as be
+    from frodo_slam_b200 import synth
+    mp = synth.MATCH_PARAMS
+    base = 8  # distinct synthetic pairs, tiled to B (inputs stay > L2: 38 MB/pair)
+    d = synth.matching_pairs(min(base, B), H_IMG, W_IMG, seed=0, device=device)
+    rep = (B + base - 1) // base
+    tile = lambda x: x.repeat((rep,) + (1,) * (x.dim() - 1))[:B].contiguous()  # noqa: E731
+    rays, pts, p0 = synth.prep_for_iter_proj(tile(d["X11"]), tile(d["X21"]))
+    D11 = tile(d["D11"]).half().contiguous()
+    D21 = tile(d["D21"]).half().reshape(B, N_PTS, -1).contiguous()
+    del d
+    out = {}
+
+    def step():
+        p, conv = be.iter_proj(rays, pts, p0, mp["max_iter"], mp["lambda_init"],
+                               mp["convergence_thresh"])
+        out["p1"] = p.long()
+        out["r"] = be.refine_matches(D11, D21, out["p1"], mp["radius"], mp["dilation_max"])
+
+    ms = timed_steps(step, steps, warmup)
+    p1 = out["p1"]
+    ms_ip = timed_steps(lambda: be.iter_proj(rays, pts, p0, mp["max_iter"], mp["lambda_init"],
+                                             mp["convergence_thresh"]), steps, 1)
+    ms_rm = timed_steps(lambda: be.refine_matches(D11, D21, p1, mp["radius"], mp["dilation_max"]),
+                        steps, 1)
+    px = B * N_PTS * steps
+    val = px / (ms * 1e-3)
+    return {
+        "metric": "px-matches/s (iter_proj+refine_matches)", "value": val, "unit": "px/s",
+        "pairs": B, "resolution": "512x384", "ms_per_step": ms / steps,
+        "iter_proj": {"px_per_s": px / (ms_ip * 1e-3),
+                      "roofline_frac": 65 * px / (ms_ip * 1e-3) / 1e9 / peak},
+        "refine_matches": {"px_per_s": px / (ms_rm * 1e-3),
+                           "roofline_frac": 130 * px / (ms_rm * 1e-3) / 1e9 / peak},
+        "roofline": {"bound": "hbm", "achieved": MATCH_BYTES_PER_PX * val / 1e9, "peak": peak,
+                     "unit": "GB/s", "frac": MATCH_BYTES_PER_PX * val / 1e9 / peak,
+                     "traffic": None},
+        "gpu_launches": 2 * steps,
+    }
+
+
+def cpu_baseline_gn(g_np, seconds=12.0):
+    """Oracle port (C, OpenMP, all host threads) on a bounded sample of the same workload:
+    per-edge accumulation of a subset of the 256 edges; iters/s extrapolated to the full graph."""
+    from frodo_slam_b200 import synth
+    from oracle import oracle
+    gp = synth.GN_PARAMS
+    cores = oracle.num_threads()
+    ie, je, _ = oracle.edge_index(g_np["ii"], g_np["jj"])
+    E = len(ie)
+    ns = min(E, 2 * cores)
+    t0 = time.perf_counter()
+    passes = 0
+    while True:
+        oracle.edge_blocks("rays", g_np["Twc"], g_np["Xs"], g_np["Cs"], ie[:ns], je[:ns],
+                           g_np["idx"][:ns], g_np["valid"][:ns], g_np["Q"][:ns], gp["sigma_ray"],
+                           gp["sigma_dist"], gp["C_conf"], gp["Q_conf"])
+        passes += 1
+        if time.perf_counter() - t0 > seconds:
+            break
+    dt = (time.perf_counter() - t0) / passes
+    t_iter = dt * E / ns
+    return {"value": 1.0 / t_iter, "unit": "iters/s", "cores": cores, "kind": "port",
+            "sample": f"{ns} of {E} edges x {N_PTS} points, {passes} passes, accumulation only "
+                      f"(solve excluded), extrapolated x{E / ns:.0f}"}
+
+
+def main_ours(args):
+    import torch.distributed as dist
+    import mast3r_slam_backends as be
+    from frodo_slam_b200 import _lib, dist as fdist, synth
+    rank, world, local = dist_env()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    barrier = (lambda: dist.barrier()) if world > 1 else None
+    peak, peak_src = measured_peak_gbs()
+    prm, gp = gn_params()
+    K, g = build_graph(dev)
+    E = g["ii"].shape[0]
+    lo, hi = fdist.edge_slice(E, rank, world)
+    idx = g["idx_ii2jj"].view(E, N_PTS)
+    valid = g["valid_match"].view(E, N_PTS)
+    Q = g["Q"].view(E, N_PTS)
+    Twc0 = g["Twc"].clone()
+    Twc = g["Twc"].clone()
+    sg = fdist.ShardedGaussNewton(prm, Twc, g["Xs"], g["Cs"], None, g["ii"], g["jj"],
+                                  idx[lo:hi].contiguous(), valid[lo:hi].contiguous(),
+                                  Q[lo:hi].contiguous(), lo, hi, gp["num_fix"])
+    iters = args.gn_iters
+
+    def step():
+        Twc.copy_(Twc0)
+        sg.solve(iters, 0.0)
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms = timed_steps(step, args.steps, args.warmup, barrier)
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    clocks = sampler.stop() if rank == 0 else None
+    assert int(sg.flags[1].item()) == iters and int(sg.flags[2].item()) == 0, "GN did not run clean"
+    value = args.steps * iters / (ms * 1e-3)
+
+    # dominant kernel alone (accumulate, no assembly): CUDA events on the launch stream
+    lib = _lib.load()
+    import ctypes
+    from frodo_slam_b200.backends import _ptr, _stream
+    Twc.copy_(Twc0)
+
+    def acc_only():
+        _lib.check(lib.frodo_gn_accumulate(
+            ctypes.byref(prm), _ptr(Twc), _ptr(g["Xs"]), _ptr(g["Cs"]), None, _ptr(sg.ii_row),
+            _ptr(sg.jj_row), _ptr(sg.idx), _ptr(sg.valid), _ptr(sg.Q), K, N_PTS, sg.E_local,
+            gp["num_fix"], None, None, None, _ptr(sg.ws), sg.nbytes, _stream()))
+
+    n_acc = max(args.steps * iters, 10)
+    ms_acc = timed_steps(acc_only, n_acc, 3) / n_acc
+    bytes_launch = GN_BYTES_PER_POINT * N_PTS * sg.E_local
+    achieved = bytes_launch / (ms_acc * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "gn_accumulate_kernel<rays>", "achieved": achieved,
+                "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "us_per_launch": ms_acc * 1e3,
+                "algorithmic_bytes_per_launch": bytes_launch,
+                "share_of_step": ms_acc * iters / (ms / args.steps)}
+    prof = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof):
+        try:
+            roofline["traffic"] = json.load(open(prof)).get("gn_accumulate_rays_bytes_per_launch")
+        except Exception:
+            pass
+
+    # end to end: host (pinned) buffers -> operator -> poses back on the host
+    host = {k: g[k].cpu().pin_memory() for k in ("Xs", "Cs", "ii", "jj")}
+    host["Twc"] = Twc0.cpu().pin_memory()
+    host["idx"] = idx[lo:hi].cpu().pin_memory()
+    host["valid"] = valid[lo:hi].cpu().pin_memory()
+    host["Q"] = Q[lo:hi].cpu().pin_memory()
+    out_host = torch.empty_like(host["Twc"]).pin_memory()
+    h2d = sum(v.numel() * v.element_size() for v in host.values())
+    d2h = out_host.numel() * out_host.element_size()
+    del sg, idx, valid, Q
+    g_full_E = E
+
+    def e2e_step():
+        d = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+        if world == 1:
+            be.gauss_newton_rays(d["Twc"], d["Xs"], d["Cs"], d["ii"], d["jj"], d["idx"],
+                                 d["valid"].view(-1, N_PTS, 1), d["Q"], gp["sigma_ray"],
+                                 gp["sigma_dist"], gp["C_conf"], gp["Q_conf"], gp["num_fix"],
+                                 iters, 0.0)
+        else:
+            s = fdist.ShardedGaussNewton(prm, d["Twc"], d["Xs"], d["Cs"], None, d["ii"], d["jj"],
+                                         d["idx"], d["valid"], d["Q"], lo, hi, gp["num_fix"])
+            s.solve(iters, 0.0)
+        out_host.copy_(d["Twc"], non_blocking=True)
+
+    e2e_steps = max(2, min(args.steps, 5))
+    ms_e2e = timed_steps(e2e_step, e2e_steps, 1, barrier)
+    t = torch.tensor([ms_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_e2e = float(t.item())
+    e2e = {"value": e2e_steps * iters / (ms_e2e * 1e-3), "unit": "iters/s",
+           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / e2e_steps,
+           "api": "mast3r_slam_backends.gauss_newton_rays" if world == 1
+                  else "frodo_slam_b200.dist.ShardedGaussNewton"}
+
+    cpu = None
+    g_np = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        g_np = {"Twc": Twc0.cpu().numpy(), "Xs": g["Xs"].cpu().numpy(), "Cs": g["Cs"].cpu().numpy(),
+                "ii": g["ii"].cpu().numpy(), "jj": g["jj"].cpu().numpy(),
+                "idx": host["idx"].numpy(), "valid": host["valid"].numpy().astype(np.uint8),
+                "Q": host["Q"].numpy()}
+    del g, host
+    torch.cuda.empty_cache()
+    matching = None
+    if not args.no_matching:
+        Bm = max(1, args.pairs // world)
+        matching = run_matching(dev, Bm, max(2, min(args.steps, 5)), 3, peak)
+        if world > 1:
+            tv = torch.tensor([matching["value"]], device=dev, dtype=torch.float64)
+            dist.all_reduce(tv, op=dist.ReduceOp.SUM)
+            matching["value"] = float(tv.item())
+            matching["pairs"] = Bm * world
+            matching["note"] = "batch split over ranks, no collective (replicas only)"
+    if g_np is not None:
+        cpu = cpu_baseline_gn(g_np)
+
+    if rank == 0:
+        line = {
+            "metric": "GN-rays iters/s, 64-KF 512x384", "value": value, "unit": "iters/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32 (fp64 assembly/solve)", "data": "synthetic",
+            "config": {"workload": "configs[2]: 64-keyframe graph, 63 chain + 65 loop-closure edges "
+                                   "both directions (E=256), 512x384 pointmaps, gauss_newton_rays, "
+                                   f"{iters} iterations per step, delta_thresh=0",
+                       "edges_per_gpu": hi - lo, "sharding": f"edges/{world} + allreduce(H,g)",
+                       "l2": "inputs larger than L2 (2.27 GB streamed per iteration)"},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
+            "gpu_launches": args.steps * (3 * iters),
+            "matching": matching,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+class _QuietStdout:
+    """The reference prints its solver log with std::cout every iteration: silence fd 1."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        self.null = os.open(os.devnull, os.O_WRONLY)
+        os.dup2(self.null, 1)
+
+    def __exit__(self, *a):
+        os.dup2(self.saved, 1)
+        os.close(self.null)
+        os.close(self.saved)
+
+
+def load_reference_backend():
+    import glob
+    import importlib.util
+    so = glob.glob(os.path.join(ROOT, "oracle", "_ref", "mast3r_slam_backends*.so"))
+    if not so:
+        return None
+    try:
+        spec = importlib.util.spec_from_file_location("mast3r_slam_backends", so[0])
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        return mod
+    except Exception:
+        return None
+
+
+def main_reference(args):
+    """Reference arm: the UNMODIFIED reference backend (oracle/_ref, its own pybind API and
+    stock CUDA + Eigen code path) on the same graph when it is built and a GPU is present;
+    otherwise the oracle port on the host cores.  Rank 0 only."""
+    rank, world, local = dist_env()
+    if rank != 0:
+        return
+    from frodo_slam_b200 import synth
+    gp = synth.GN_PARAMS
+    iters = args.gn_iters
+    ref = load_reference_backend() if torch.cuda.is_available() else None
+    dev = torch.device("cuda", local) if torch.cuda.is_available() else torch.device("cpu")
+    if torch.cuda.is_available():
+        torch.cuda.set_device(local)
+    K, g = build_graph(dev)
+    E = g["ii"].shape[0]
+    g_np = {"Twc": g["Twc"].cpu().numpy(), "Xs": g["Xs"].cpu().numpy(), "Cs": g["Cs"].cpu().numpy(),
+            "ii": g["ii"].cpu().numpy(), "jj": g["jj"].cpu().numpy(),
+            "idx": g["idx_ii2jj"].view(E, N_PTS).cpu().numpy(),
+            "valid": g["valid_match"].view(E, N_PTS).cpu().numpy().astype(np.uint8),
+            "Q": g["Q"].view(E, N_PTS).cpu().numpy()}
+    cfg = {"workload": "configs[2]: 64-keyframe graph, 63 chain + 65 loop-closure edges both "
+                       f"directions (E=256), 512x384 pointmaps, gauss_newton_rays, {iters} "
+                       "iterations per step, delta_thresh=0"}
+    if ref is not None:
+        Twc0 = g["Twc"].clone()
+
+        def step():
+            T = Twc0.clone()
+            ref.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"],
+                                  g["valid_match"], g["Q"], gp["sigma_ray"], gp["sigma_dist"],
+                                  gp["C_conf"], gp["Q_conf"], gp["num_fix"], iters, 0.0)
+
+        with _QuietStdout():
+            ms = timed_steps(step, args.steps, max(1, min(args.warmup, 2)))
+        value = args.steps * iters / (ms * 1e-3)
+        kind, cores = "reference", os.cpu_count()
+        sample = ("full workload on the same GPU through the reference's own CUDA kernels + host "
+                  "Eigen solve (the reference has no CPU implementation of this path)")
+        cfg["device"] = torch.cuda.get_device_name(local)
+        steps_done = args.steps
+    else:
+        del g
+        cb = cpu_baseline_gn(g_np, seconds=10.0 * max(1, args.steps))
+        value, kind, cores, sample = cb["value"], cb["kind"], cb["cores"], cb["sample"]
+        ms, steps_done = 1e3 * iters / value, 1
+    line = {"impl": "reference", "metric": "GN-rays iters/s, 64-KF 512x384", "value": value,
+            "unit": "iters/s", "n_gpus": 1, "steps": steps_done, "warmup": args.warmup,
+            "ms_per_step": ms / steps_done, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32 (fp64 assembly/solve)", "data": "synthetic",
+            "config": cfg,
+            "cpu_baseline": {"value": value, "unit": "iters/s", "cores": cores, "kind": kind,
+                             "sample": sample},
+            "e2e": {"value": value, "unit": "iters/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0}}
+    if ref is not None and not args.no_cpu_baseline:
+        line["cpu_port"] = cpu_baseline_gn(g_np, seconds=10.0)
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--gn-iters", type=int, default=10)
+    ap.add_argument("--pairs", type=int, default=256, help="frame pairs of the matching sweep")
+    ap.add_argument("--no-matching", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        main_reference(args)
+    else:
+        main_ours(args)
+
+
+if __name__ == "__main__":
+    main()

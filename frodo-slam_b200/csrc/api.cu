@@ -113,7 +113,7 @@ int frodo_gn_accumulate(const frodo_gn_params* params, const float* Twc, const f
   FRODO_ARG_CHECK(params != nullptr && K >= 1 && N >= 0 && E >= 0 && num_fix >= 0);
   FRODO_ARG_CHECK(params->mode != FRODO_GN_CALIB || Kmat != nullptr);
   FRODO_ARG_CHECK(E <= 65535);
-  FRODO_ARG_CHECK(Hg != nullptr && workspace != nullptr);
+  FRODO_ARG_CHECK(workspace != nullptr);
   FRODO_ARG_CHECK(workspace_bytes >= gn_carve_workspace(nullptr, K, E, N, nullptr));
   FRODO_ARG_CHECK(E == 0 || (Twc && Xs && Cs && ii_row && jj_row && idx_ii2jj && valid_match && Q));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -123,6 +123,7 @@ int frodo_gn_accumulate(const frodo_gn_params* params, const float* Twc, const f
   int rc = launch_gn_accumulate(*params, Twc, Xs, Cs, Kmat, ii_row, jj_row, idx_ii2jj,
                                 valid_match, Q, N, E, ws.partials, ws.tickets, eb, done, s);
   if (rc) return rc;
+  if (Hg == nullptr) return FRODO_OK;  // per-edge blocks only
   return launch_gn_assemble(eb, ii_row, jj_row, E, K, num_fix, Hg, done, s);
 }
 

@@ -1,0 +1,91 @@
+"""Edge-sharded multi-GPU Gauss-Newton: one process per GPU, keyframe
+poses/pointmaps replicated, the directed edges split into contiguous per-rank slices.
+Each iteration every rank accumulates its edges into a local dense fp64 [H | g], the
+systems are summed with one all-reduce (NCCL over NVLink on GPUs, gloo on CPU-only
+test runs of the host logic), and every rank runs the identical Cholesky solve and
+pose retraction -- bit-identical inputs give bit-identical poses, so no broadcast of
+dx is needed.  The reference has no multi-GPU path."""
+import ctypes
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from .backends import _gn_validate, _ptr, _stream
+
+
+def edge_slice(num_edges, rank, world):
+    """Contiguous balanced slice [lo, hi) of the edge list owned by `rank`."""
+    base, rem = divmod(num_edges, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+class ShardedGaussNewton:
+    """Holds the per-rank buffers of one keyframe graph so repeated solves (and CUDA-event
+    timing) do not reallocate.  `params` is a backends.GnParams; tensors are this rank's
+    device copies: Twc/Xs/Cs(/K) replicated, ii/jj FULL edge lists (the id ranking must see
+    every keyframe), idx/valid/Q only the local slice [lo, hi)."""
+
+    def __init__(self, params, Twc, Xs, Cs, K, ii, jj, idx_local, valid_local, Q_local, lo, hi,
+                 num_fix, group=None):
+        self.params, self.group = params, group
+        self.Twc, self.Xs, self.Cs, self.K = Twc, Xs, Cs, K
+        self.lo, self.hi, self.num_fix = lo, hi, num_fix
+        self.idx, self.valid, self.Q = idx_local, valid_local, Q_local
+        dev = Twc.device
+        self.num_kf, self.N = Xs.shape[0], Xs.shape[1]
+        E = ii.shape[0]
+        self.E_local = hi - lo
+        lib = self.lib = _lib.load()
+        n = self.n = 7 * (self.num_kf - num_fix)
+        with torch.cuda.device(dev):
+            self.nbytes = lib.frodo_gn_workspace_bytes(self.num_kf, max(self.E_local, 1), self.N)
+            self.ws = torch.empty(self.nbytes, dtype=torch.uint8, device=dev)
+            self.Hg = torch.empty((n + 1) * n, dtype=torch.float64, device=dev)
+            self.dx = torch.zeros((self.num_kf - num_fix, 7), dtype=torch.float32, device=dev)
+            self.flags = torch.zeros(4, dtype=torch.int32, device=dev)  # [done, iters, fails, -]
+            ii_row = torch.empty(E, dtype=torch.int32, device=dev)
+            jj_row = torch.empty(E, dtype=torch.int32, device=dev)
+            _lib.check(lib.frodo_gn_edge_index(_ptr(ii), _ptr(jj), E, _ptr(ii_row), _ptr(jj_row),
+                                               None, _stream()))
+            self.ii_row = ii_row[lo:hi].contiguous()
+            self.jj_row = jj_row[lo:hi].contiguous()
+
+    def solve(self, max_iter, delta_thresh):
+        lib, dev = self.lib, self.Twc.device
+        with torch.cuda.device(dev):
+            st = _stream()
+            self.flags.zero_()
+            _lib.check(lib.frodo_gn_workspace_init(_ptr(self.ws), self.nbytes, self.num_kf,
+                                                   max(self.E_local, 1), self.N, st))
+            done = ctypes.c_void_p(self.flags.data_ptr())
+            info = ctypes.c_void_p(self.flags.data_ptr() + 4)
+            for _ in range(max_iter):
+                _lib.check(lib.frodo_gn_accumulate(
+                    ctypes.byref(self.params), _ptr(self.Twc), _ptr(self.Xs), _ptr(self.Cs),
+                    _ptr(self.K), _ptr(self.ii_row), _ptr(self.jj_row), _ptr(self.idx),
+                    _ptr(self.valid), _ptr(self.Q), self.num_kf, self.N, self.E_local,
+                    self.num_fix, _ptr(self.Hg), None, done, _ptr(self.ws), self.nbytes, st))
+                if dist.is_initialized() and dist.get_world_size(self.group) > 1:
+                    dist.all_reduce(self.Hg, op=dist.ReduceOp.SUM, group=self.group)
+                _lib.check(lib.frodo_gn_solve_retract(
+                    _ptr(self.Hg), _ptr(self.Twc), _ptr(self.dx), self.num_kf, self.num_fix,
+                    float(delta_thresh), done, info, _ptr(self.ws), self.nbytes, st))
+        return self.dx
+
+
+def gauss_newton_sharded(params, Twc, Xs, Cs, K, ii, jj, idx_ii2jj, valid_match, Q, num_fix,
+                         max_iter, delta_thresh, group=None):
+    """Multi-GPU counterpart of gauss_newton_{rays,points,calib}: every rank passes the FULL
+    edge tensors (as the single-GPU op takes them) and works on its own slice.  Updates Twc in
+    place on every rank, returns [dx]."""
+    _gn_validate(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, K)
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    E, N = ii.shape[0], Xs.shape[1]
+    lo, hi = edge_slice(E, rank, world)
+    s = ShardedGaussNewton(params, Twc, Xs, Cs, K, ii, jj, idx_ii2jj.view(E, N)[lo:hi],
+                           valid_match.view(E, N)[lo:hi], Q.view(E, N)[lo:hi], lo, hi, num_fix,
+                           group)
+    return [s.solve(max_iter, delta_thresh)]

@@ -100,7 +100,8 @@ int frodo_gn_edge_index(const int64_t* ii, const int64_t* jj, int E, int32_t* ii
  * gn_kernels.cu:576-907, 1936-2204, 2295-2607) over the E edges given, followed
  * by assembly (SparseBlock::update_lhs/rhs, :72-122) into the dense fp64 system
  *   Hg = [ H (n x n, row-major) | g (n) ],  n = 7*(K - num_fix)
- * which is OVERWRITTEN (not accumulated into).  Edge rows come from
+ * which is OVERWRITTEN (not accumulated into); Hg == NULL skips the assembly and
+ * only produces edge_blocks.  Edge rows come from
  * frodo_gn_edge_index.  edge_blocks (may be NULL) receives per-edge [E,35] f64:
  * the 28 upper-triangular entries of H_jj (row-major) then g_j; by
  * construction H_ii = H_jj = -H_ij = -H_ji and g_i = -g_j.
