@@ -32,22 +32,25 @@ size_t gn_carve_workspace(void* base, int K, int E, int N, GnWorkspace* ws) {
     off = align_up(off + bytes, 256);
     return o;
   };
+  // K-dependent regions first: frodo_gn_solve_retract locates them without knowing E, N
+  const size_t o_ch = take(gn_chol_scratch_bytes((int)n));
+  const size_t o_hg = take((n + 1) * n * sizeof(double));
   const size_t o_ii = take(Ez * sizeof(int32_t));
   const size_t o_jj = take(Ez * sizeof(int32_t));
   const size_t o_sc = take(8 * sizeof(int32_t));
   const size_t o_tk = take(Ez * sizeof(int32_t));
   const size_t o_pt = take(Ez * max_chunks * kGnBlock * sizeof(float));
   const size_t o_eb = take(Ez * kGnBlock * sizeof(double));
-  const size_t o_hg = take((n + 1) * n * sizeof(double));
   if (base != nullptr && ws != nullptr) {
     char* b = static_cast<char*>(base);
+    ws->chol = reinterpret_cast<double*>(b + o_ch);
+    ws->Hg = reinterpret_cast<double*>(b + o_hg);
     ws->ii_row = reinterpret_cast<int32_t*>(b + o_ii);
     ws->jj_row = reinterpret_cast<int32_t*>(b + o_jj);
     ws->scalars = reinterpret_cast<int32_t*>(b + o_sc);
     ws->tickets = reinterpret_cast<int32_t*>(b + o_tk);
     ws->partials = reinterpret_cast<float*>(b + o_pt);
     ws->edge_blocks = reinterpret_cast<double*>(b + o_eb);
-    ws->Hg = reinterpret_cast<double*>(b + o_hg);
     ws->bytes = off;
   }
   return off;
@@ -130,11 +133,13 @@ int frodo_gn_accumulate(const frodo_gn_params* params, const float* Twc, const f
 int frodo_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fix,
                            float delta_thresh, int32_t* done, int32_t* info, void* workspace,
                            size_t workspace_bytes, frodo_stream_t stream) {
-  (void)workspace;
-  (void)workspace_bytes;
   FRODO_ARG_CHECK(K >= 1 && num_fix >= 0 && num_fix <= K);
   FRODO_ARG_CHECK(K == num_fix || (Hg && Twc && dx));
-  return launch_gn_solve_retract(Hg, Twc, dx, K, num_fix, delta_thresh, done, info,
+  // the Cholesky tile scratch is the first region of the workspace (depends on K only)
+  double* chol = nullptr;
+  if (workspace != nullptr && workspace_bytes >= gn_chol_scratch_bytes(7 * K))
+    chol = static_cast<double*>(workspace);
+  return launch_gn_solve_retract(Hg, Twc, dx, K, num_fix, delta_thresh, done, info, chol,
                                  static_cast<cudaStream_t>(stream));
 }
 
@@ -173,7 +178,8 @@ int frodo_gauss_newton(const frodo_gn_params* params, float* Twc, const float* X
                              valid_match, Q, K, N, E, num_fix, ws.Hg, ws.edge_blocks, done,
                              workspace, workspace_bytes, stream);
     if (rc) return rc;
-    rc = launch_gn_solve_retract(ws.Hg, Twc, dx, K, num_fix, delta_thresh, done, winfo, s);
+    rc = launch_gn_solve_retract(ws.Hg, Twc, dx, K, num_fix, delta_thresh, done, winfo, ws.chol,
+                                 s);
     if (rc) return rc;
   }
   if (info != nullptr)

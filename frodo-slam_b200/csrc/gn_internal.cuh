@@ -17,6 +17,7 @@ struct GnWorkspace {
   float* partials;     // [E * nchunks * 35]
   double* edge_blocks; // [E * 35]
   double* Hg;          // [(n+1) * n]
+  double* chol;        // tile scratch of the cluster Cholesky (gn_chol_scratch_bytes)
   size_t bytes;
 };
 // Carves `base` (may be NULL to only compute sizes).  Returns total bytes.
@@ -32,6 +33,8 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
 int launch_gn_assemble(const double* edge_blocks, const int32_t* ii_row, const int32_t* jj_row,
                        int E, int K, int num_fix, double* Hg, const int32_t* done, cudaStream_t s);
 int launch_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fix,
-                            float delta_thresh, int32_t* done, int32_t* info, cudaStream_t s);
+                            float delta_thresh, int32_t* done, int32_t* info, double* chol_scratch,
+                            cudaStream_t s);
+size_t gn_chol_scratch_bytes(int n);
 
 }  // namespace frodo
