@@ -101,16 +101,38 @@ assemble_kernel(const double* __restrict__ edge_blocks, const int32_t* __restric
     sidx = 28 + (tid - 49);
   }
   const bool is_g = (tid >= 49 && tid < 56);
-  for (int e = 0; e < E; ++e) {
-    const int io = ii_row[e] - num_fix, jo = jj_row[e] - num_fix;
-    if (tid < 49) {
-      const int coef = (io == a && io == b) + (jo == a && jo == b) - (io == a && jo == b) -
-                       (jo == a && io == b);
-      if (coef != 0) acc += (double)coef * edge_blocks[(size_t)e * kGnBlock + sidx];
-    } else if (is_g && a == b) {
-      const int coef = (jo == a) - (io == a);
-      if (coef != 0) acc += (double)coef * edge_blocks[(size_t)e * kGnBlock + sidx];
+  // The 64 threads classify 64 edges at a time; ballots give the (few) edges that touch
+  // this block, visited in edge order by every accumulating thread.
+  __shared__ signed char s_ch[64], s_cg[64];
+  __shared__ unsigned s_mask[2];
+  for (int base = 0; base < E; base += 64) {
+    const int e = base + tid;
+    int ch = 0, cg = 0;
+    if (e < E) {
+      const int io = ii_row[e] - num_fix, jo = jj_row[e] - num_fix;
+      ch = (io == a && io == b) + (jo == a && jo == b) - (io == a && jo == b) -
+           (jo == a && io == b);
+      if (a == b) cg = (jo == a) - (io == a);
     }
+    s_ch[tid] = (signed char)ch;
+    s_cg[tid] = (signed char)cg;
+    const unsigned m = __ballot_sync(0xffffffffu, ch != 0 || cg != 0);
+    if ((tid & 31) == 0) s_mask[tid >> 5] = m;
+    __syncthreads();
+    if (tid < 56) {
+#pragma unroll
+      for (int w = 0; w < 2; ++w) {
+        unsigned mm = s_mask[w];
+        while (mm) {
+          const int k = w * 32 + __ffs(mm) - 1;
+          mm &= mm - 1;
+          const int coef = is_g ? s_cg[k] : s_ch[k];
+          if (coef != 0)
+            acc += (double)coef * edge_blocks[(size_t)(base + k) * kGnBlock + sidx];
+        }
+      }
+    }
+    __syncthreads();
   }
   if (tid < 49) {
     Hg[(size_t)(7 * a + r) * n + (7 * b + c)] = acc;

@@ -36,5 +36,8 @@ int launch_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fi
                             float delta_thresh, int32_t* done, int32_t* info, double* chol_scratch,
                             cudaStream_t s);
 size_t gn_chol_scratch_bytes(int n);
+int launch_chol_cluster(double* Hg, float* Twc, float* dx, int K, int num_fix, float delta_thresh,
+                        int32_t* done, int32_t* info, double* chol_scratch, int* handled,
+                        cudaStream_t s);
 
 }  // namespace frodo
