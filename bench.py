@@ -242,7 +242,7 @@ def main_ours(args):
 
     def acc_only():
         _lib.check(lib.frodo_gn_accumulate(
-            ctypes.byref(prm), _ptr(Twc), _ptr(g["Xs"]), _ptr(g["Cs"]), None, _ptr(sg.ii_row),
+            ctypes.byref(prm), _ptr(Twc), _ptr(g["Xs"]), _ptr(g["Cs"]), None, sg.xc, _ptr(sg.ii_row),
             _ptr(sg.jj_row), _ptr(sg.idx), _ptr(sg.valid), _ptr(sg.Q), K, N_PTS, sg.E_local,
             gp["num_fix"], None, None, None, _ptr(sg.ws), sg.nbytes, _stream()))
 
@@ -250,7 +250,7 @@ def main_ours(args):
     ms_acc = timed_steps(acc_only, n_acc, 3) / n_acc
     bytes_launch = GN_BYTES_PER_POINT * N_PTS * sg.E_local
     achieved = bytes_launch / (ms_acc * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "gn_accumulate_kernel<rays>", "achieved": achieved,
+    roofline = {"bound": "hbm", "kernel": "gn_accumulate_rays_packed_kernel", "achieved": achieved,
                 "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None, "us_per_launch": ms_acc * 1e3,
                 "algorithmic_bytes_per_launch": bytes_launch,

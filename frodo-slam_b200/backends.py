@@ -203,8 +203,13 @@ def gn_system(params, Twc, Xs, Cs, K, ii, jj, idx_ii2jj, valid_match, Q, num_fix
         _lib.check(lib.frodo_gn_workspace_init(_ptr(ws), nbytes, num_kf, E, N, st))
         _lib.check(lib.frodo_gn_edge_index(_ptr(ii), _ptr(jj), E, _ptr(ii_row), _ptr(jj_row), None,
                                            st))
+        xc = None
+        if params.mode == GN_RAYS and N % 16 == 0 and E > 0:
+            off = lib.frodo_gn_workspace_packed_offset(num_kf, E, N)
+            xc = ctypes.c_void_p(ws.data_ptr() + off)
+            _lib.check(lib.frodo_gn_pack_points(_ptr(Xs), _ptr(Cs), num_kf, N, xc, st))
         _lib.check(lib.frodo_gn_accumulate(
-            ctypes.byref(params), _ptr(Twc), _ptr(Xs), _ptr(Cs), _ptr(K), _ptr(ii_row),
+            ctypes.byref(params), _ptr(Twc), _ptr(Xs), _ptr(Cs), _ptr(K), xc, _ptr(ii_row),
             _ptr(jj_row), _ptr(idx_ii2jj), _ptr(valid_match), _ptr(Q), num_kf, N, E, int(num_fix),
             _ptr(Hg), _ptr(eb), None, _ptr(ws), nbytes, st))
     return Hg[:n * n].view(n, n), Hg[n * n:], eb, ii_row, jj_row

@@ -25,7 +25,7 @@ static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; 
 size_t gn_carve_workspace(void* base, int K, int E, int N, GnWorkspace* ws) {
   const size_t Ez = (size_t)(E > 0 ? E : 1);
   const size_t n = (size_t)7 * (size_t)(K > 0 ? K : 1);
-  const size_t max_chunks = ((size_t)(N > 0 ? N : 1) + 1023) / 1024;
+  const size_t max_chunks = ((size_t)(N > 0 ? N : 1) + 511) / 512;  // >= tiles per edge
   size_t off = 0;
   auto take = [&](size_t bytes) {
     size_t o = off;
@@ -41,6 +41,8 @@ size_t gn_carve_workspace(void* base, int K, int E, int N, GnWorkspace* ws) {
   const size_t o_tk = take(Ez * sizeof(int32_t));
   const size_t o_pt = take(Ez * max_chunks * kGnBlock * sizeof(float));
   const size_t o_eb = take(Ez * kGnBlock * sizeof(double));
+  // last: the pointmaps repacked as float4 (x,y,z,c), same size as Xs + Cs
+  const size_t o_pk = take((size_t)(K > 0 ? K : 1) * (size_t)(N > 0 ? N : 1) * 4 * sizeof(float));
   if (base != nullptr && ws != nullptr) {
     char* b = static_cast<char*>(base);
     ws->chol = reinterpret_cast<double*>(b + o_ch);
@@ -51,8 +53,10 @@ size_t gn_carve_workspace(void* base, int K, int E, int N, GnWorkspace* ws) {
     ws->tickets = reinterpret_cast<int32_t*>(b + o_tk);
     ws->partials = reinterpret_cast<float*>(b + o_pt);
     ws->edge_blocks = reinterpret_cast<double*>(b + o_eb);
+    ws->packed = reinterpret_cast<float*>(b + o_pk);
     ws->bytes = off;
   }
+  if (ws != nullptr) ws->packed_off = o_pk;
   return off;
 }
 
@@ -107,8 +111,23 @@ int frodo_gn_edge_index(const int64_t* ii, const int64_t* jj, int E, int32_t* ii
                               static_cast<cudaStream_t>(stream));
 }
 
+size_t frodo_gn_workspace_packed_offset(int K, int E, int N) {
+  GnWorkspace ws;
+  gn_carve_workspace(nullptr, K, E, N, &ws);
+  return ws.packed_off;
+}
+
+int frodo_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float* XC,
+                         frodo_stream_t stream) {
+  FRODO_ARG_CHECK(K >= 0 && N >= 0);
+  FRODO_ARG_CHECK(K == 0 || N == 0 || (Xs && Cs && XC));
+  FRODO_ARG_CHECK((reinterpret_cast<uintptr_t>(XC) & 15) == 0);
+  return launch_gn_pack_points(Xs, Cs, K, N, XC, static_cast<cudaStream_t>(stream));
+}
+
 int frodo_gn_accumulate(const frodo_gn_params* params, const float* Twc, const float* Xs,
-                        const float* Cs, const float* Kmat, const int32_t* ii_row,
+                        const float* Cs, const float* Kmat, const float* XC,
+                        const int32_t* ii_row,
                         const int32_t* jj_row, const int64_t* idx_ii2jj,
                         const uint8_t* valid_match, const float* Q, int K, int N, int E,
                         int num_fix, double* Hg, double* edge_blocks, const int32_t* done,
@@ -123,7 +142,7 @@ int frodo_gn_accumulate(const frodo_gn_params* params, const float* Twc, const f
   GnWorkspace ws;
   gn_carve_workspace(workspace, K, E, N, &ws);
   double* eb = edge_blocks ? edge_blocks : ws.edge_blocks;
-  int rc = launch_gn_accumulate(*params, Twc, Xs, Cs, Kmat, ii_row, jj_row, idx_ii2jj,
+  int rc = launch_gn_accumulate(*params, Twc, Xs, Cs, Kmat, XC, ii_row, jj_row, idx_ii2jj,
                                 valid_match, Q, N, E, ws.partials, ws.tickets, eb, done, s);
   if (rc) return rc;
   if (Hg == nullptr) return FRODO_OK;  // per-edge blocks only
@@ -173,8 +192,15 @@ int frodo_gauss_newton(const frodo_gn_params* params, float* Twc, const float* X
   int32_t* winfo = ws.scalars + 2;
   rc = launch_gn_edge_index(ii, jj, E, ws.ii_row, ws.jj_row, ws.scalars, s);
   if (rc) return rc;
+  // rays fast path: repack the pointmaps once per solve (they do not change across iterations)
+  const float* XC = nullptr;
+  if (params->mode == FRODO_GN_RAYS && E > 0 && N > 0 && (N % 16) == 0 && max_iter > 0) {
+    rc = launch_gn_pack_points(Xs, Cs, K, N, ws.packed, s);
+    if (rc) return rc;
+    XC = ws.packed;
+  }
   for (int it = 0; it < max_iter; ++it) {
-    rc = frodo_gn_accumulate(params, Twc, Xs, Cs, Kmat, ws.ii_row, ws.jj_row, idx_ii2jj,
+    rc = frodo_gn_accumulate(params, Twc, Xs, Cs, Kmat, XC, ws.ii_row, ws.jj_row, idx_ii2jj,
                              valid_match, Q, K, N, E, num_fix, ws.Hg, ws.edge_blocks, done,
                              workspace, workspace_bytes, stream);
     if (rc) return rc;

@@ -13,6 +13,7 @@
 // -> fp64 across CTAs; M S M^T in fp64.
 #include "common.cuh"
 #include "gn_internal.cuh"
+#include "ptx_async.cuh"
 
 namespace frodo {
 
@@ -191,56 +192,66 @@ __device__ __forceinline__ void point_terms(const EdgeConst& c, float (&S)[28], 
 }
 
 // ---------------------------------------------------------------------------
-// rays, fast path (N % 4 == 0, 16-byte aligned inputs): every thread streams 4
-// consecutive points per step with 128-bit loads, and the weighted outer
-// products run on the packed fp32 pipe (FFMA2, two fp32 lanes per issue slot).
-// A residual row is x~ = [x0..x5 | e]: 3 register pairs X0,X1,X2 and the scalar
-// e; with WX_p = w X_p the row adds
-//   diagonal blocks   Dp  += (WX_p.x, WX_p.y) (x) X_p      (2 FFMA2, one lane dup)
-//   off-diagonal      Opq += (WX_p.x, WX_p.y) (x) X_q      (2 FFMA2)
-//   gradient          Ep  += WX_p * e                      (1 FFMA2)
-// The distance row [r0 r1 r2 | nj | e3] has its own small accumulator set.
-// Weights: w = huber(|e| sqrt(q)/sigma) q/sigma^2 = min(1, 1.345 rsqrt(t)) wq
-// with t = wq e^2, wq = q/sigma^2 (same value, no sqrt(q)).
+// rays, fast path.  The weighted outer products run on the packed fp32 pipe (FFMA2, two
+// fp32 lanes per issue slot).  A ray row a (a = 0,1,2) of the local Jacobian is
+//   x = [ d_a0 d_a1 d_a2 | c_a ],  d = (I - r r^T)/|P|,  c_a = row a of -[r]x
+// and c_a has exactly two non-zeros (+-r_p, +-r_q).  With the residual e_a appended it is
+// packed into three register pairs without padding:
+//   T0 = (d_a0, d_a1)   T1 = (d_a2, e_a)   M = (r_p, r_q)   (signs applied at unpack)
+// and adds, with W* = w * pair:
+//   TT  = W0.x*T0, W0.y*T0          -> S00 S01 (S10) S11        shared by all rows
+//   TU  = W0.x*T1, W0.y*T1          -> S02 v0 S12 v1             shared
+//   UU  = W1.x*T1                   -> S22 v2                    shared
+//   TM  = W0.x*M, W0.y*M            -> S0p S0q S1p S1q           per row
+//   UM  = W1.x*M, W1.y*M            -> S2p S2q vp vq             per row
+//   MM  = WM.x*M, WM.y*M            -> Spp Spq (Sqp) Sqq         per row
+// i.e. 11 FFMA2 + 3 FMUL2 per row.  The distance row [r0 r1 r2 | nj | e3] uses the same
+// T0/T1 accumulators with T0 = (r0,r1), T1 = (r2,e3) plus the nj column.
+// Weights: w = huber(|e| sqrt(q)/sigma) q/sigma^2 = min(1, 1.345 rsqrt(t)) wq with
+// t = wq e^2, wq = q/sigma^2 (same value as gn_kernels.cu:214-217,730-741, no sqrt(q)).
 // ---------------------------------------------------------------------------
 struct RaysAcc {
-  float2 Da[3], Db[3];   // diagonal blocks: Da = (S[2p][2p], S[2p][2p+1]), Db = (dup, S[2p+1][2p+1])
-  float2 Oa[3], Ob[3];   // blocks (0,1),(0,2),(1,2): rows 2p / 2p+1, columns 2q, 2q+1
-  float2 E[3];           // v[2p], v[2p+1]
-  float2 Ra, Rb, Rab_a, Rab_b, Re_a, Re_b;  // distance row: pairs A=(r0,r1), B=(r2,nj)
-  float2 Rda;            // (A.x*A.x, A.x*A.y)
-  float2 Rdb;            // (A.y*A.x, A.y*A.y)
+  float2 TTa, TTb, TUa, TUb, UU;  // shared T-block accumulators
+  float2 TMa[3], TMb[3], UMa[3], UMb[3], MMa[3], MMb[3];  // per ray row
+  float2 N6a, N6b;  // (S06, S16), (S26, v6)
+  float n66;
 };
 
 __device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
 __device__ __forceinline__ float2 bc(float a) { return make_float2(a, a); }
 
+__device__ __forceinline__ float rsqrt_fast(float x) {
+  float y;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ float huber_w(float wq, float e) {
   // min(1, 1.345 / (|e| sqrt(wq))) * wq ; wq = 0 -> 0
   const float t = wq * e * e;
-  return fminf(1.0f, 1.345f * rsqrtf(t)) * wq;
+  return fminf(1.0f, 1.345f * rsqrt_fast(t)) * wq;
 }
 
-__device__ __forceinline__ void rays_row(RaysAcc& A, float w, float2 X0, float2 X1, float2 X2,
-                                         float e) {
-  const float2 W0 = __fmul2_rn(bc(w), X0);
-  const float2 W1 = __fmul2_rn(bc(w), X1);
-  const float2 W2 = __fmul2_rn(bc(w), X2);
-  A.Da[0] = __ffma2_rn(bc(W0.x), X0, A.Da[0]);
-  A.Db[0] = __ffma2_rn(bc(W0.y), X0, A.Db[0]);
-  A.Da[1] = __ffma2_rn(bc(W1.x), X1, A.Da[1]);
-  A.Db[1] = __ffma2_rn(bc(W1.y), X1, A.Db[1]);
-  A.Da[2] = __ffma2_rn(bc(W2.x), X2, A.Da[2]);
-  A.Db[2] = __ffma2_rn(bc(W2.y), X2, A.Db[2]);
-  A.Oa[0] = __ffma2_rn(bc(W0.x), X1, A.Oa[0]);
-  A.Ob[0] = __ffma2_rn(bc(W0.y), X1, A.Ob[0]);
-  A.Oa[1] = __ffma2_rn(bc(W0.x), X2, A.Oa[1]);
-  A.Ob[1] = __ffma2_rn(bc(W0.y), X2, A.Ob[1]);
-  A.Oa[2] = __ffma2_rn(bc(W1.x), X2, A.Oa[2]);
-  A.Ob[2] = __ffma2_rn(bc(W1.y), X2, A.Ob[2]);
-  A.E[0] = __ffma2_rn(W0, bc(e), A.E[0]);
-  A.E[1] = __ffma2_rn(W1, bc(e), A.E[1]);
-  A.E[2] = __ffma2_rn(W2, bc(e), A.E[2]);
+__device__ __forceinline__ void t_block(RaysAcc& A, float2 W0, float2 W1, float2 T0, float2 T1) {
+  A.TTa = __ffma2_rn(bc(W0.x), T0, A.TTa);
+  A.TTb = __ffma2_rn(bc(W0.y), T0, A.TTb);
+  A.TUa = __ffma2_rn(bc(W0.x), T1, A.TUa);
+  A.TUb = __ffma2_rn(bc(W0.y), T1, A.TUb);
+  A.UU = __ffma2_rn(bc(W1.x), T1, A.UU);
+}
+
+template <int ROW>
+__device__ __forceinline__ void rays_row(RaysAcc& A, float w, float2 T0, float2 T1, float2 M) {
+  const float2 W0 = __fmul2_rn(bc(w), T0);
+  const float2 W1 = __fmul2_rn(bc(w), T1);
+  const float2 WM = __fmul2_rn(bc(w), M);
+  t_block(A, W0, W1, T0, T1);
+  A.TMa[ROW] = __ffma2_rn(bc(W0.x), M, A.TMa[ROW]);
+  A.TMb[ROW] = __ffma2_rn(bc(W0.y), M, A.TMb[ROW]);
+  A.UMa[ROW] = __ffma2_rn(bc(W1.x), M, A.UMa[ROW]);
+  A.UMb[ROW] = __ffma2_rn(bc(W1.y), M, A.UMb[ROW]);
+  A.MMa[ROW] = __ffma2_rn(bc(WM.x), M, A.MMa[ROW]);
+  A.MMb[ROW] = __ffma2_rn(bc(WM.y), M, A.MMb[ROW]);
 }
 
 struct RaysConst {
@@ -256,11 +267,11 @@ __device__ __forceinline__ void rays_point(const RaysConst& c, RaysAcc& A, float
   const float P1 = fmaf(c.M[3], xj0, fmaf(c.M[4], xj1, fmaf(c.M[5], xj2, c.t[1])));
   const float P2 = fmaf(c.M[6], xj0, fmaf(c.M[7], xj1, fmaf(c.M[8], xj2, c.t[2])));
   const float n2j = fmaf(P0, P0, fmaf(P1, P1, P2 * P2));
-  const float a = rsqrtf(n2j);
+  const float a = rsqrt_fast(n2j);
   const float nj = n2j * a;
   const float r0 = P0 * a, r1 = P1 * a, r2 = P2 * a;
   const float n2i = fmaf(xi0, xi0, fmaf(xi1, xi1, xi2 * xi2));
-  const float bi = rsqrtf(n2i);
+  const float bi = rsqrt_fast(n2i);
   const float ni = n2i * bi;
   const float e0 = fmaf(-xi0, bi, r0);
   const float e1 = fmaf(-xi1, bi, r1);
@@ -272,63 +283,70 @@ __device__ __forceinline__ void rays_point(const RaysConst& c, RaysAcc& A, float
   const float w0 = huber_w(wr, e0), w1 = huber_w(wr, e1), w2 = huber_w(wr, e2);
   const float w3 = huber_w(wd, e3);
   // d r / d P = (I - r r^T) / |P|
-  const float na = -a;
-  const float d00 = fmaf(na * r0, r0, a), d11 = fmaf(na * r1, r1, a), d22 = fmaf(na * r2, r2, a);
-  const float d01 = na * r0 * r1, d02 = na * r0 * r2, d12 = na * r1 * r2;
-  rays_row(A, w0, f2(d00, d01), f2(d02, 0.0f), f2(r2, -r1), e0);
-  rays_row(A, w1, f2(d01, d11), f2(d12, -r2), f2(0.0f, r0), e1);
-  rays_row(A, w2, f2(d02, d12), f2(d22, r1), f2(-r0, 0.0f), e2);
+  const float s0 = -a * r0, s1 = -a * r1, s2 = -a * r2;
+  const float d00 = fmaf(s0, r0, a), d11 = fmaf(s1, r1, a), d22 = fmaf(s2, r2, a);
+  const float d01 = s0 * r1, d02 = s0 * r2, d12 = s1 * r2;
+  // c_0 = (0, r2, -r1)  c_1 = (-r2, 0, r0)  c_2 = (r1, -r0, 0): magnitudes only, signs at unpack
+  rays_row<0>(A, w0, f2(d00, d01), f2(d02, e0), f2(r1, r2));
+  rays_row<1>(A, w1, f2(d01, d11), f2(d12, e1), f2(r0, r2));
+  rays_row<2>(A, w2, f2(d02, d12), f2(d22, e2), f2(r0, r1));
   // distance row [r0 r1 r2 | nj | e3]
-  const float2 XA = f2(r0, r1), XB = f2(r2, nj);
-  const float2 WA = __fmul2_rn(bc(w3), XA), WB = __fmul2_rn(bc(w3), XB);
-  A.Rda = __ffma2_rn(bc(WA.x), XA, A.Rda);
-  A.Rdb = __ffma2_rn(bc(WA.y), XA, A.Rdb);
-  A.Ra = __ffma2_rn(bc(WB.x), XB, A.Ra);
-  A.Rb = __ffma2_rn(bc(WB.y), XB, A.Rb);
-  A.Rab_a = __ffma2_rn(bc(WA.x), XB, A.Rab_a);
-  A.Rab_b = __ffma2_rn(bc(WA.y), XB, A.Rab_b);
-  A.Re_a = __ffma2_rn(WA, bc(e3), A.Re_a);
-  A.Re_b = __ffma2_rn(WB, bc(e3), A.Re_b);
+  {
+    const float2 T0 = f2(r0, r1), T1 = f2(r2, e3);
+    const float2 W0 = __fmul2_rn(bc(w3), T0), W1 = __fmul2_rn(bc(w3), T1);
+    t_block(A, W0, W1, T0, T1);
+    A.N6a = __ffma2_rn(W0, bc(nj), A.N6a);
+    A.N6b = __ffma2_rn(W1, bc(nj), A.N6b);
+    A.n66 = fmaf(w3 * nj, nj, A.n66);
+  }
 }
 
 __host__ __device__ constexpr int tri(int n, int m) { return n * 7 - n * (n - 1) / 2 + (m - n); }
 
 // Folds the packed accumulators into the canonical 28 upper-triangular entries + 7.
+// Row a's rotation entries sit at columns 3..5 with
+//   c_0: col 4 = +r2, col 5 = -r1 ; c_1: col 3 = -r2, col 5 = +r0 ; c_2: col 3 = +r1, col 4 = -r0
+// and the packed pairs hold M_0 = (r1, r2), M_1 = (r0, r2), M_2 = (r0, r1).
 __device__ __forceinline__ void rays_unpack(const RaysAcc& A, float (&S)[28], float (&v)[7]) {
-#pragma unroll
-  for (int l = 0; l < 28; ++l) S[l] = 0.f;
-  S[tri(0, 0)] = A.Da[0].x + A.Rda.x;
-  S[tri(0, 1)] = A.Da[0].y + A.Rda.y;
-  S[tri(1, 1)] = A.Db[0].y + A.Rdb.y;
-  S[tri(2, 2)] = A.Da[1].x + A.Ra.x;
-  S[tri(2, 3)] = A.Da[1].y;
-  S[tri(3, 3)] = A.Db[1].y;
-  S[tri(4, 4)] = A.Da[2].x;
-  S[tri(4, 5)] = A.Da[2].y;
-  S[tri(5, 5)] = A.Db[2].y;
-  S[tri(0, 2)] = A.Oa[0].x + A.Rab_a.x;
-  S[tri(0, 3)] = A.Oa[0].y;
-  S[tri(1, 2)] = A.Ob[0].x + A.Rab_b.x;
-  S[tri(1, 3)] = A.Ob[0].y;
-  S[tri(0, 4)] = A.Oa[1].x;
-  S[tri(0, 5)] = A.Oa[1].y;
-  S[tri(1, 4)] = A.Ob[1].x;
-  S[tri(1, 5)] = A.Ob[1].y;
-  S[tri(2, 4)] = A.Oa[2].x;
-  S[tri(2, 5)] = A.Oa[2].y;
-  S[tri(3, 4)] = A.Ob[2].x;
-  S[tri(3, 5)] = A.Ob[2].y;
-  S[tri(0, 6)] = A.Rab_a.y;
-  S[tri(1, 6)] = A.Rab_b.y;
-  S[tri(2, 6)] = A.Ra.y;
-  S[tri(6, 6)] = A.Rb.y;
-  v[0] = A.E[0].x + A.Re_a.x;
-  v[1] = A.E[0].y + A.Re_a.y;
-  v[2] = A.E[1].x + A.Re_b.x;
-  v[3] = A.E[1].y;
-  v[4] = A.E[2].x;
-  v[5] = A.E[2].y;
-  v[6] = A.Re_b.y;
+  S[tri(0, 0)] = A.TTa.x;
+  S[tri(0, 1)] = A.TTa.y;
+  S[tri(1, 1)] = A.TTb.y;
+  S[tri(0, 2)] = A.TUa.x;
+  S[tri(1, 2)] = A.TUb.x;
+  S[tri(2, 2)] = A.UU.x;
+  v[0] = A.TUa.y;
+  v[1] = A.TUb.y;
+  v[2] = A.UU.y;
+  // T x M: S[n][col]
+  //   row0: r1 -> col5 (-), r2 -> col4 (+) ; row1: r0 -> col5 (+), r2 -> col3 (-)
+  //   row2: r0 -> col4 (-), r1 -> col3 (+)
+  S[tri(0, 3)] = -A.TMa[1].y + A.TMa[2].y;
+  S[tri(0, 4)] = A.TMa[0].y - A.TMa[2].x;
+  S[tri(0, 5)] = -A.TMa[0].x + A.TMa[1].x;
+  S[tri(1, 3)] = -A.TMb[1].y + A.TMb[2].y;
+  S[tri(1, 4)] = A.TMb[0].y - A.TMb[2].x;
+  S[tri(1, 5)] = -A.TMb[0].x + A.TMb[1].x;
+  S[tri(2, 3)] = -A.UMa[1].y + A.UMa[2].y;
+  S[tri(2, 4)] = A.UMa[0].y - A.UMa[2].x;
+  S[tri(2, 5)] = -A.UMa[0].x + A.UMa[1].x;
+  v[3] = -A.UMb[1].y + A.UMb[2].y;
+  v[4] = A.UMb[0].y - A.UMb[2].x;
+  v[5] = -A.UMb[0].x + A.UMb[1].x;
+  // M x M
+  S[tri(3, 3)] = A.MMb[1].y + A.MMb[2].y;   // r2 r2 (row1) + r1 r1 (row2)
+  S[tri(4, 4)] = A.MMb[0].y + A.MMa[2].x;   // r2 r2 (row0) + r0 r0 (row2)
+  S[tri(5, 5)] = A.MMa[0].x + A.MMa[1].x;   // r1 r1 (row0) + r0 r0 (row1)
+  S[tri(3, 4)] = -A.MMa[2].y;               // row2: (+r1)(-r0)
+  S[tri(3, 5)] = -A.MMa[1].y;               // row1: (+r0)(-r2)
+  S[tri(4, 5)] = -A.MMa[0].y;               // row0: (-r1)(+r2)
+  S[tri(0, 6)] = A.N6a.x;
+  S[tri(1, 6)] = A.N6a.y;
+  S[tri(2, 6)] = A.N6b.x;
+  S[tri(3, 6)] = 0.f;
+  S[tri(4, 6)] = 0.f;
+  S[tri(5, 6)] = 0.f;
+  S[tri(6, 6)] = A.n66;
+  v[6] = A.N6b.y;
 }
 
 // Adjoint map M of pose i (7x7, fp64):  Jj = M x  (apply_Sim3_adj_inv, :319-339)
@@ -360,34 +378,49 @@ __device__ void adjoint_matrix(const Sim3f& Ti, double* M /*[49]*/) {
 // CTA reduction of the 35 per-thread sums (warp shuffles, one smem stage), fp32 partial
 // per chunk; the last CTA of the edge (ticket) sums the chunks in fixed order in fp64 and
 // applies the adjoint: A = M S M^T, g = M v.
+// Slot (e, chunk) of `partials` is at (e * stride + chunk); stride >= nchunks.
+template <int THREADS>
 __device__ __forceinline__ void edge_epilogue(float (&S)[28], float (&v)[7], const Sim3f& Ti,
-                                              int e, int chunk, int nchunks,
+                                              int e, int chunk, int nchunks, int stride,
                                               float* __restrict__ partials,
                                               int32_t* __restrict__ tickets,
                                               double* __restrict__ edge_blocks) {
-  __shared__ float warp_part[kThreads / 32][kGnBlock];
+  __shared__ float warp_part[THREADS / 32][kGnBlock];
   __shared__ int is_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  {
+    // entries 0..31 (28 of S, v[0..3]): reduce-scatter, lane m ends with the warp total of
+    // entry m (31 exchanges); v[4..6]: butterflies.
+    float a[32];
 #pragma unroll
-  for (int l = 0; l < 28; ++l) {
-    float x = S[l];
+    for (int l = 0; l < 28; ++l) a[l] = S[l];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-    if (lane == 0) warp_part[warp][l] = x;
-  }
+    for (int l = 0; l < 4; ++l) a[28 + l] = v[l];
 #pragma unroll
-  for (int l = 0; l < 7; ++l) {
-    float x = v[l];
+    for (int half = 16; half >= 1; half >>= 1) {
+      const bool up = (lane & half) != 0;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-    if (lane == 0) warp_part[warp][28 + l] = x;
+      for (int i = 0; i < half; ++i) {
+        const float send = up ? a[i] : a[i + half];
+        const float keep = up ? a[i + half] : a[i];
+        a[i] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+      }
+    }
+    warp_part[warp][lane] = a[0];
+#pragma unroll
+    for (int l = 4; l < 7; ++l) {
+      float x = v[l];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+      if (lane == 0) warp_part[warp][28 + l] = x;
+    }
   }
   __syncthreads();
-  float* __restrict__ my_part = partials + ((size_t)e * nchunks + chunk) * kGnBlock;
+  float* __restrict__ my_part = partials + ((size_t)e * stride + chunk) * kGnBlock;
   if (threadIdx.x < kGnBlock) {
     float x = 0.f;
 #pragma unroll
-    for (int w = 0; w < kThreads / 32; ++w) x += warp_part[w][threadIdx.x];
+    for (int w = 0; w < THREADS / 32; ++w) x += warp_part[w][threadIdx.x];
     my_part[threadIdx.x] = x;
   }
   __threadfence();
@@ -406,7 +439,7 @@ __device__ __forceinline__ void edge_epilogue(float (&S)[28], float (&v)[7], con
   __shared__ double Md[49];
   __shared__ double MS[49];
   if (threadIdx.x < kGnBlock) {
-    const float* p = partials + (size_t)e * nchunks * kGnBlock + threadIdx.x;
+    const float* p = partials + (size_t)e * stride * kGnBlock + threadIdx.x;
     double acc = 0.0;
     for (int ch = 0; ch < nchunks; ++ch) acc += (double)__ldcg(p + (size_t)ch * kGnBlock);
     Sd[threadIdx.x] = acc;
@@ -523,25 +556,94 @@ gn_accumulate_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
       point_terms<MODE>(c, S, v, Xi[r], Xj[r], q[r], ci[r], cj[r], vm[r], ind[r]);
   }
 
-  edge_epilogue(S, v, Ti, e, chunk, nchunks, partials, tickets, edge_blocks);
+  edge_epilogue<kThreads>(S, v, Ti, e, chunk, nchunks, nchunks, partials, tickets, edge_blocks);
 }
 
-// rays fast path: see the comment above RaysAcc.  Requires N % 4 == 0, pts_per_cta % 1024 == 0
-// and 16-byte aligned Xs, Cs, idx, Q (valid_match 4-byte aligned).
+// ---------------------------------------------------------------------------
+// rays fast path kernel: see the comment above RaysAcc for the arithmetic.
+// Inputs: the keyframe pointmaps repacked once per solve into XC [K][N] float4 (x,y,z,c)
+// (frodo_gn_pack_points), so that the data-dependent gather of frame i is ONE aligned
+// 16-byte load per point instead of four 4-byte loads (4x fewer L1 requests and sectors:
+// the unpacked gather ran at ~23 sectors per warp request and kept the L1 tag stage busy
+// for the whole kernel, profiles/r1_ncu_accumulate.md).
+// Data movement per CTA (one edge, `pts_per_cta` points, tiles of 1024 points):
+//   * the streamed arrays of a tile (idx 8 KB, XC of frame j 16 KB, Q 4 KB, valid 1 KB:
+//     contiguous, read once) are fetched by the TMA unit (cp.async.bulk, SASS UBLKCP) into a
+//     3-stage shared-memory ring, one transaction mbarrier per stage;
+//   * lanes work on consecutive points (thread t: points t, t+256, t+512, t+768 of the
+//     tile), so a gather request covers 16 consecutive-ish sectors;
+//   * 4-slot gather ring refilled in place: right after point s of tile t is consumed, the
+//     gather of point s of tile t+1 is issued into the same registers, so every gather has
+//     a whole tile (~650 instructions x 4 warps per scheduler) to arrive;
+//   * a stage is refilled with tile t+3 after the block-wide barrier that follows its last
+//     reader.
+// Requires N % 16 == 0, pts_per_cta % 1024 == 0 and 16-byte aligned XC, idx, Q, valid.
+// ---------------------------------------------------------------------------
+constexpr int kTilePts = 1024;
+constexpr int kStages = 3;
+constexpr int kOffIdx = 0;                       // int64  [1024]
+constexpr int kOffXC = kOffIdx + kTilePts * 8;   // float4 [1024]  frame j (x,y,z,c)
+constexpr int kOffQ = kOffXC + kTilePts * 16;    // float  [1024]
+constexpr int kOffVm = kOffQ + kTilePts * 4;     // uint8  [1024]
+constexpr int kStageBytes = kOffVm + kTilePts;   // 29 bytes per point
+static_assert(kStageBytes % 128 == 0, "stage alignment");
+static_assert(kTilePts == 4 * kThreads, "the point loop is unrolled 4x per tile");
+
+__global__ void pack_points_kernel(const float* __restrict__ Xs, const float* __restrict__ Cs,
+                                   float4* __restrict__ XC, size_t total) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += stride) {
+    const float* x = Xs + p * 3;
+    XC[p] = make_float4(__ldg(x), __ldg(x + 1), __ldg(x + 2), __ldg(Cs + p));
+  }
+}
+
 __global__ void __launch_bounds__(kThreads, 2)
-gn_accumulate_rays_v2_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
-                             const float* __restrict__ Xs, const float* __restrict__ Cs,
-                             const int32_t* __restrict__ ii_row,
-                             const int32_t* __restrict__ jj_row, const int64_t* __restrict__ idx,
-                             const uint8_t* __restrict__ valid_match, const float* __restrict__ Q,
-                             int N, int pts_per_cta, float* __restrict__ partials,
-                             int32_t* __restrict__ tickets, double* __restrict__ edge_blocks,
-                             const int32_t* __restrict__ done) {
+gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
+                                 const float4* __restrict__ XC,
+                                 const int32_t* __restrict__ ii_row,
+                                 const int32_t* __restrict__ jj_row,
+                                 const int64_t* __restrict__ idx,
+                                 const uint8_t* __restrict__ valid_match,
+                                 const float* __restrict__ Q, int N, int pts_per_cta,
+                                 float* __restrict__ partials, int32_t* __restrict__ tickets,
+                                 double* __restrict__ edge_blocks,
+                                 const int32_t* __restrict__ done) {
   if (done != nullptr && *done != 0) return;
+  extern __shared__ __align__(128) unsigned char stage_raw[];
+  __shared__ __align__(8) uint64_t full_bar[kStages];
   const int e = blockIdx.y;
   const int chunk = blockIdx.x;
   const int nchunks = gridDim.x;
+  const int tid = threadIdx.x;
   const int ix = ii_row[e], jx = jj_row[e];
+  const int k_begin = chunk * pts_per_cta;
+  const int k_end = min(N, k_begin + pts_per_cta);
+  const int ntile = (k_end - k_begin + kTilePts - 1) / kTilePts;
+  const float4* __restrict__ XCi = XC + (size_t)ix * N;
+  const float4* gXCj = XC + (size_t)jx * N;
+  const int64_t* gIdx = idx + (size_t)e * N;
+  const uint8_t* gVm = valid_match + (size_t)e * N;
+  const float* gQ = Q + (size_t)e * N;
+
+  // producer: one thread arms the stage barrier and issues the four bulk copies of tile t
+  auto issue_tile = [&](int t) {
+    const int k0 = k_begin + t * kTilePts;
+    const uint32_t np = (uint32_t)min(kTilePts, k_end - k0);
+    unsigned char* st = stage_raw + (size_t)(t % kStages) * kStageBytes;
+    uint64_t* bar = &full_bar[t % kStages];
+    ptx::mbar_arrive_expect_tx(bar, np * 29u);
+    ptx::bulk_g2s(st + kOffIdx, gIdx + k0, np * 8u, bar);
+    ptx::bulk_g2s(st + kOffXC, gXCj + k0, np * 16u, bar);
+    ptx::bulk_g2s(st + kOffQ, gQ + k0, np * 4u, bar);
+    ptx::bulk_g2s(st + kOffVm, gVm + k0, np, bar);
+  };
+  if (tid == 0) {
+    for (int s = 0; s < kStages; ++s) ptx::mbar_init(&full_bar[s], 1);
+    ptx::mbar_fence_init();
+    for (int t = 0; t < kStages && t < ntile; ++t) issue_tile(t);
+  }
+
   const Sim3f Ti = load_pose(Twc, ix);
   const Sim3f Tj = load_pose(Twc, jx);
   RaysConst c;
@@ -568,82 +670,126 @@ gn_accumulate_rays_v2_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
   RaysAcc A;
   {
     const float2 z = make_float2(0.f, 0.f);
+    A.TTa = A.TTb = A.TUa = A.TUb = A.UU = A.N6a = A.N6b = z;
 #pragma unroll
-    for (int p = 0; p < 3; ++p) A.Da[p] = A.Db[p] = A.Oa[p] = A.Ob[p] = A.E[p] = z;
-    A.Ra = A.Rb = A.Rab_a = A.Rab_b = A.Re_a = A.Re_b = A.Rda = A.Rdb = z;
+    for (int p = 0; p < 3; ++p)
+      A.TMa[p] = A.TMb[p] = A.UMa[p] = A.UMb[p] = A.MMa[p] = A.MMb[p] = z;
+    A.n66 = 0.f;
   }
-  const float* __restrict__ Xi_base = Xs + (size_t)ix * N * 3;
-  const float* __restrict__ Ci_base = Cs + (size_t)ix * N;
-  const float4* __restrict__ Xj4 = reinterpret_cast<const float4*>(Xs + (size_t)jx * N * 3);
-  const float4* __restrict__ Cj4 = reinterpret_cast<const float4*>(Cs + (size_t)jx * N);
-  const longlong2* __restrict__ idx2 = reinterpret_cast<const longlong2*>(idx + (size_t)e * N);
-  const uint32_t* __restrict__ vm4 = reinterpret_cast<const uint32_t*>(valid_match + (size_t)e * N);
-  const float4* __restrict__ Q4 = reinterpret_cast<const float4*>(Q + (size_t)e * N);
+  __syncthreads();  // barriers initialised before anyone waits on them
 
-  const int k_begin = chunk * pts_per_cta;
-  const int k_end = min(N, k_begin + pts_per_cta);
-  for (int k = k_begin + threadIdx.x * 4; k < k_end; k += kThreads * 4) {
-    const int g4 = k >> 2;  // index of this group of 4 points
-    // streamed, read-once per-edge data (evict-first) and frame-j points
-    const uint32_t vmw = __ldcs(vm4 + g4);
-    const longlong2 ia = __ldcs(idx2 + 2 * g4), ib = __ldcs(idx2 + 2 * g4 + 1);
-    const float4 q4 = __ldcs(Q4 + g4);
-    const float4 cj4 = __ldg(Cj4 + g4);
-    const float4 xa = __ldg(Xj4 + 3 * g4), xb = __ldg(Xj4 + 3 * g4 + 1),
-                 xc = __ldg(Xj4 + 3 * g4 + 2);
-    long long ind[4] = {ia.x, ia.y, ib.x, ib.y};
-    bool vm[4];
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      vm[r] = ((vmw >> (8 * r)) & 0xffu) != 0;
-      if (!vm[r]) ind[r] = 0;  // gn_kernels.cu:677
+  auto stage_of = [&](int t) { return stage_raw + (size_t)(t % kStages) * kStageBytes; };
+  auto tile_np = [&](int t) { return min(kTilePts, k_end - (k_begin + t * kTilePts)); };
+  // frame-i gather of point (t, s) of this thread (stage t must be full)
+  auto gather = [&](const unsigned char* st, int np, int s, float4& G) {
+    const int p = s * kThreads + tid;
+    if (p < np) {
+      long long ind = reinterpret_cast<const long long*>(st + kOffIdx)[p];
+      if (st[kOffVm + p] == 0) ind = 0;  // gn_kernels.cu:677
+      G = __ldg(XCi + ind);
     }
-    // gathers from frame i
-    float xi[4][3], ci[4];
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      const float* px = Xi_base + (size_t)ind[r] * 3;
-      xi[r][0] = __ldg(px);
-      xi[r][1] = __ldg(px + 1);
-      xi[r][2] = __ldg(px + 2);
-      ci[r] = __ldg(Ci_base + ind[r]);
+  };
+  auto compute = [&](const unsigned char* st, int np, int s, const float4& G) {
+    const int p = s * kThreads + tid;
+    if (p < np) {
+      const float4 xj = reinterpret_cast<const float4*>(st + kOffXC)[p];
+      const float q = reinterpret_cast<const float*>(st + kOffQ)[p];
+      rays_point(c, A, G.x, G.y, G.z, xj.x, xj.y, xj.z, q, G.w, xj.w, st[kOffVm + p] != 0);
     }
-    rays_point(c, A, xi[0][0], xi[0][1], xi[0][2], xa.x, xa.y, xa.z, q4.x, ci[0], cj4.x, vm[0]);
-    rays_point(c, A, xi[1][0], xi[1][1], xi[1][2], xa.w, xb.x, xb.y, q4.y, ci[1], cj4.y, vm[1]);
-    rays_point(c, A, xi[2][0], xi[2][1], xi[2][2], xb.z, xb.w, xc.x, q4.z, ci[2], cj4.z, vm[2]);
-    rays_point(c, A, xi[3][0], xi[3][1], xi[3][2], xc.y, xc.z, xc.w, q4.w, ci[3], cj4.w, vm[3]);
+  };
+
+  float4 G[4];
+  uint32_t phase_bits = 0;  // bit s = parity to wait for on stage s
+  auto wait_stage = [&](int t) {
+    const int s = t % kStages;
+    ptx::mbar_wait(&full_bar[s], (phase_bits >> s) & 1u);
+    phase_bits ^= 1u << s;
+  };
+  if (ntile > 0) {
+    wait_stage(0);
+    const unsigned char* st = stage_of(0);
+    const int np = tile_np(0);
+#pragma unroll
+    for (int s = 0; s < 4; ++s) gather(st, np, s, G[s]);
+  }
+  for (int t = 0; t < ntile; ++t) {
+    const bool more = t + 1 < ntile;
+    if (more) wait_stage(t + 1);
+    const unsigned char* st = stage_of(t);
+    const unsigned char* st1 = stage_of(t + 1);
+    const int np = tile_np(t), np1 = more ? tile_np(t + 1) : 0;
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      compute(st, np, s, G[s]);
+      gather(st1, np1, s, G[s]);
+    }
+    __syncthreads();  // every reader of stage t % kStages is done
+    if (tid == 0 && t + kStages < ntile) issue_tile(t + kStages);
   }
   float S[28], v[7];
   rays_unpack(A, S, v);
-  edge_epilogue(S, v, Ti, e, chunk, nchunks, partials, tickets, edge_blocks);
+  edge_epilogue<kThreads>(S, v, Ti, e, chunk, nchunks, nchunks, partials, tickets, edge_blocks);
 }
 
 }  // namespace
 
+// Points per accumulate CTA: minimises ceil(waves) * (points + fixed per-CTA cost) over a few
+// multiples of the 1024-point tile (2 CTAs per SM; the fixed cost ~ 1500 points covers the
+// pipeline fill and the reduction epilogue).
 int gn_pts_per_cta(int E, int N) {
-  long long want = ((long long)N * (long long)(E > 0 ? E : 1)) / (kNumSMs * 16);
-  long long p = ((want + 1023) / 1024) * 1024;
-  if (p < 1024) p = 1024;
-  if (p > 8192) p = 8192;
-  return (int)p;
+  const long long cand[] = {4096, 8192, 12288, 16384, 24576, 32768};
+  const double slots = 2.0 * kNumSMs;
+  long long best = 4096;
+  double best_cost = 1e300;
+  for (long long ppc : cand) {
+    const long long nch = ((long long)(N > 0 ? N : 1) + ppc - 1) / ppc;
+    const double waves = (double)(nch * (long long)(E > 0 ? E : 1)) / slots;
+    const double rounds = waves <= 1.0 ? 1.0 : (double)(long long)(waves + 0.999999);
+    const long long eff = ppc < N ? ppc : ((N + 1023) / 1024) * 1024;
+    const double cost = rounds * ((double)eff + 1500.0);
+    if (cost < best_cost) {
+      best_cost = cost;
+      best = ppc;
+    }
+  }
+  return (int)best;
+}
+
+int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float* XC,
+                          cudaStream_t s) {
+  const size_t total = (size_t)K * (size_t)N;
+  if (total == 0) return FRODO_OK;
+  const int blocks = (int)((total + 255) / 256 < (size_t)(8 * kNumSMs) ? (total + 255) / 256
+                                                                       : (size_t)(8 * kNumSMs));
+  pack_points_kernel<<<blocks, 256, 0, s>>>(Xs, Cs, reinterpret_cast<float4*>(XC), total);
+  FRODO_CUDA_TRY(cudaGetLastError());
+  return FRODO_OK;
 }
 
 int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const float* Xs,
-                         const float* Cs, const float* Kmat, const int32_t* ii_row,
-                         const int32_t* jj_row, const int64_t* idx, const uint8_t* valid,
-                         const float* Q, int N, int E, float* partials, int32_t* tickets,
-                         double* edge_blocks, const int32_t* done, cudaStream_t s) {
+                         const float* Cs, const float* Kmat, const float* XC,
+                         const int32_t* ii_row, const int32_t* jj_row, const int64_t* idx,
+                         const uint8_t* valid, const float* Q, int N, int E, float* partials,
+                         int32_t* tickets, double* edge_blocks, const int32_t* done,
+                         cudaStream_t s) {
   if (E == 0) return FRODO_OK;
   const int ppc = gn_pts_per_cta(E, N);
   const int nchunks = (N + ppc - 1) / ppc;
   dim3 grid(nchunks > 0 ? nchunks : 1, E);
-  const bool aligned16 = ((reinterpret_cast<uintptr_t>(Xs) | reinterpret_cast<uintptr_t>(Cs) |
-                           reinterpret_cast<uintptr_t>(idx) | reinterpret_cast<uintptr_t>(Q)) & 15) == 0 &&
-                         (reinterpret_cast<uintptr_t>(valid) & 3) == 0;
-  if (prm.mode == FRODO_GN_RAYS && (N % 4) == 0 && aligned16) {
-    gn_accumulate_rays_v2_kernel<<<grid, kThreads, 0, s>>>(prm, Twc, Xs, Cs, ii_row, jj_row, idx,
-                                                          valid, Q, N, ppc, partials, tickets,
-                                                          edge_blocks, done);
+  const bool aligned16 =
+      ((reinterpret_cast<uintptr_t>(XC) | reinterpret_cast<uintptr_t>(idx) |
+        reinterpret_cast<uintptr_t>(Q) | reinterpret_cast<uintptr_t>(valid)) & 15) == 0;
+  if (prm.mode == FRODO_GN_RAYS && XC != nullptr && (N % 16) == 0 && aligned16) {
+    static bool attr_set = false;
+    const size_t smem = (size_t)kStages * kStageBytes;
+    if (!attr_set) {
+      FRODO_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_rays_packed_kernel,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_set = true;
+    }
+    gn_accumulate_rays_packed_kernel<<<grid, kThreads, smem, s>>>(
+        prm, Twc, reinterpret_cast<const float4*>(XC), ii_row, jj_row, idx, valid, Q, N, ppc,
+        partials, tickets, edge_blocks, done);
     FRODO_CUDA_TRY(cudaGetLastError());
     return FRODO_OK;
   }

@@ -18,6 +18,8 @@ struct GnWorkspace {
   double* edge_blocks; // [E * 35]
   double* Hg;          // [(n+1) * n]
   double* chol;        // tile scratch of the cluster Cholesky (gn_chol_scratch_bytes)
+  float* packed;       // [K * N * 4] pointmaps as float4 (x,y,z,c), frodo_gn_pack_points
+  size_t packed_off;   // byte offset of `packed` inside the workspace
   size_t bytes;
 };
 // Carves `base` (may be NULL to only compute sizes).  Returns total bytes.
@@ -25,8 +27,12 @@ size_t gn_carve_workspace(void* base, int K, int E, int N, GnWorkspace* ws);
 
 int launch_gn_edge_index(const int64_t* ii, const int64_t* jj, int E, int32_t* ii_row,
                          int32_t* jj_row, int32_t* n_unique, cudaStream_t s);
+int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float* XC,
+                          cudaStream_t s);
+// XC: pointmaps packed by launch_gn_pack_points ([K][N] float4), or NULL.
 int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const float* Xs,
-                         const float* Cs, const float* Kmat, const int32_t* ii_row,
+                         const float* Cs, const float* Kmat, const float* XC,
+                         const int32_t* ii_row,
                          const int32_t* jj_row, const int64_t* idx, const uint8_t* valid,
                          const float* Q, int N, int E, float* partials, int32_t* tickets,
                          double* edge_blocks, const int32_t* done, cudaStream_t s);

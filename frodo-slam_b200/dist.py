@@ -51,6 +51,11 @@ class ShardedGaussNewton:
                                                None, _stream()))
             self.ii_row = ii_row[lo:hi].contiguous()
             self.jj_row = jj_row[lo:hi].contiguous()
+            # rays fast path: pointmaps repacked as float4 inside the workspace, once per solve
+            self.xc = None
+            if params.mode == _lib.GN_RAYS and self.N % 16 == 0 and self.E_local > 0:
+                off = lib.frodo_gn_workspace_packed_offset(self.num_kf, max(self.E_local, 1), self.N)
+                self.xc = ctypes.c_void_p(self.ws.data_ptr() + off)
 
     def solve(self, max_iter, delta_thresh):
         lib, dev = self.lib, self.Twc.device
@@ -61,10 +66,13 @@ class ShardedGaussNewton:
                                                    max(self.E_local, 1), self.N, st))
             done = ctypes.c_void_p(self.flags.data_ptr())
             info = ctypes.c_void_p(self.flags.data_ptr() + 4)
+            if self.xc is not None and max_iter > 0:
+                _lib.check(lib.frodo_gn_pack_points(_ptr(self.Xs), _ptr(self.Cs), self.num_kf,
+                                                    self.N, self.xc, st))
             for _ in range(max_iter):
                 _lib.check(lib.frodo_gn_accumulate(
                     ctypes.byref(self.params), _ptr(self.Twc), _ptr(self.Xs), _ptr(self.Cs),
-                    _ptr(self.K), _ptr(self.ii_row), _ptr(self.jj_row), _ptr(self.idx),
+                    _ptr(self.K), self.xc, _ptr(self.ii_row), _ptr(self.jj_row), _ptr(self.idx),
                     _ptr(self.valid), _ptr(self.Q), self.num_kf, self.N, self.E_local,
                     self.num_fix, _ptr(self.Hg), None, done, _ptr(self.ws), self.nbytes, st))
                 if dist.is_initialized() and dist.get_world_size(self.group) > 1:

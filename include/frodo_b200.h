@@ -90,6 +90,16 @@ size_t frodo_gn_workspace_bytes(int K, int E, int N);
 int frodo_gn_workspace_init(void* workspace, size_t workspace_bytes, int K, int E, int N,
                             frodo_stream_t stream);
 
+/* Rays fast path: repacks the keyframe pointmaps Xs [K,N,3] and confidences Cs [K,N] into
+ * XC [K,N] float4 (x,y,z,c), 16-byte aligned, so that the data-dependent gather of
+ * ray_align_kernel (gn_kernels.cu:677-681,714) is one aligned 16-byte load per point.  The
+ * pointmaps do not change across Gauss-Newton iterations: pack once per solve and hand XC
+ * to frodo_gn_accumulate.  frodo_gn_workspace_packed_offset gives the byte offset of a
+ * K*N*16-byte region reserved for XC inside a workspace of frodo_gn_workspace_bytes. */
+int frodo_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float* XC,
+                         frodo_stream_t stream);
+size_t frodo_gn_workspace_packed_offset(int K, int E, int N);
+
 /* get_unique_kf_idx + create_inds (gn_kernels.cu:203-212): writes, for every
  * edge, the row of its two keyframes among the sorted unique ids of cat(ii,jj)
  * (ii_row, jj_row: [E] i32) and the number of unique ids (n_unique: [1] i32). */
@@ -105,10 +115,13 @@ int frodo_gn_edge_index(const int64_t* ii, const int64_t* jj, int E, int32_t* ii
  * frodo_gn_edge_index.  edge_blocks (may be NULL) receives per-edge [E,35] f64:
  * the 28 upper-triangular entries of H_jj (row-major) then g_j; by
  * construction H_ii = H_jj = -H_ij = -H_ji and g_i = -g_j.
+ * XC_packed (may be NULL): output of frodo_gn_pack_points for these Xs, Cs; enables the
+ * fast rays kernel (needs N % 16 == 0), otherwise Xs / Cs are read directly.
  * `done` (device int32, may be NULL): when non-zero at kernel time the pass is
  * skipped (convergence reached, see frodo_gn_solve_retract). */
 int frodo_gn_accumulate(const frodo_gn_params* params, const float* Twc, const float* Xs,
-                        const float* Cs, const float* Kmat, const int32_t* ii_row,
+                        const float* Cs, const float* Kmat, const float* XC_packed,
+                        const int32_t* ii_row,
                         const int32_t* jj_row, const int64_t* idx_ii2jj,
                         const uint8_t* valid_match, const float* Q, int K, int N, int E,
                         int num_fix, double* Hg, double* edge_blocks, const int32_t* done,
