@@ -332,7 +332,7 @@ def main_ours(args):
                        "edges_per_gpu": hi - lo, "sharding": f"edges/{world} + allreduce(H,g)",
                        "l2": "inputs larger than L2 (2.27 GB streamed per iteration)"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
-            "gpu_launches": args.steps * (3 * iters),
+            "gpu_launches": args.steps * (1 + 3 * iters),  # pack + (accumulate, assemble, solve)/iter
             "matching": matching,
         }
         print(json.dumps(line))
