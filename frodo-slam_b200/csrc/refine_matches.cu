@@ -7,7 +7,10 @@
 // are visited in the reference order (dilation high->low, u outer, v inner,
 // strict '>' keeps the first maximum, max_score starts at 0 for fp16 and at
 // FLT_MIN for fp32, :48).
+#include <limits.h>
+
 #include "common.cuh"
+#include "ptx_async.cuh"
 
 namespace frodo {
 
@@ -104,6 +107,243 @@ refine_f16_kernel(const __half* __restrict__ D11, const __half* __restrict__ D21
   scores[t] = max_score;
 }
 
+// ---------------------------------------------------------------------------------------
+// Tile-staged variant (the hot one): a CTA owns a 32x16 patch of query pixels, finds the
+// bounding box of their search centres, and stages that box plus the level-dil_max halo of
+// D11 in shared memory with one cp.async.bulk per tile row (the AoS rows of a box are
+// contiguous in global memory).  A candidate row is then one conflict-free LDS.128 per 16
+// bytes (lane stride = one pixel = 6F/8 banks x 4, which tiles the 32 banks per quarter
+// warp for F = 24) instead of a line-granular L1 gather; candidates that fall outside the
+// staged box (incoherent centres, box clipped to the shared-memory capacity) read global
+// memory, so the result never depends on the staging.  Scores, visiting order and
+// comparisons are those of refine_f16_kernel above.
+constexpr int kTilePatchW = 32, kTilePatchH = 32, kTileThreads = kTilePatchW * kTilePatchH;
+constexpr int kTileSmemBytes = 225 * 1024;
+
+template <int F>
+__device__ __forceinline__ void load_row_f16(uint4 (&r)[F / 8], const unsigned char* tile,
+                                             const __half* __restrict__ img, int u, int v,
+                                             int tu0, int tv0, int TW, int TH, int pitch,
+                                             int W) {
+  const int ru = u - tu0, rv = v - tv0;
+  if ((unsigned)ru < (unsigned)TW && (unsigned)rv < (unsigned)TH) {
+    const uint4* p = reinterpret_cast<const uint4*>(tile + (size_t)(rv * pitch + ru) * (F * 2));
+#pragma unroll
+    for (int blk = 0; blk < F / 8; ++blk) r[blk] = p[blk];
+  } else {
+    const uint4* p = reinterpret_cast<const uint4*>(img + ((size_t)v * W + (size_t)u) * F);
+#pragma unroll
+    for (int blk = 0; blk < F / 8; ++blk) r[blk] = __ldg(p + blk);
+  }
+}
+
+// Scores two candidate rows held in registers; lane halves (lo, hi) = (row a, row b).
+template <int F>
+__device__ __forceinline__ __half2 score_rows_f16(const __half2 (&q2)[F / 2],
+                                                  const uint4 (&a)[F / 8],
+                                                  const uint4 (&b)[F / 8]) {
+  __half2 s = __float2half2_rn(0.0f);
+#pragma unroll
+  for (int blk = 0; blk < F / 8; ++blk) {
+    const unsigned aw[4] = {a[blk].x, a[blk].y, a[blk].z, a[blk].w};
+    const unsigned bw[4] = {b[blk].x, b[blk].y, b[blk].z, b[blk].w};
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+      const __half2 av = *reinterpret_cast<const __half2*>(&aw[m]);
+      const __half2 bv = *reinterpret_cast<const __half2*>(&bw[m]);
+      const __half2 qv = q2[blk * 4 + m];
+      s = __hadd2_rn(s, __hmul2_rn(__low2half2(qv), __lows2half2(av, bv)));
+      s = __hadd2_rn(s, __hmul2_rn(__high2half2(qv), __highs2half2(av, bv)));
+    }
+  }
+  return s;
+}
+
+// One search level whose whole (2R+1)^2 lattice lies inside the staged tile (the common,
+// interior case): no bounds tests, candidate addresses are compile-time multiples of the two
+// lattice strides.  `best` receives the index of the new maximum (untouched if none).
+template <int F, int R>
+__device__ __forceinline__ void level_in_tile(const __half2 (&q2)[F / 2],
+                                              const unsigned char* base, int step_u, int step_v,
+                                              __half& max_score, int& best) {
+  constexpr int S = 2 * R + 1, NC = S * S;
+#pragma unroll
+  for (int c = 0; c < NC; c += 2) {
+    constexpr int kLast = NC - 1;
+    const int cb = c + 1 < NC ? c + 1 : kLast;
+    const uint4* pa = reinterpret_cast<const uint4*>(base + (c / S) * step_u + (c % S) * step_v);
+    const uint4* pb = reinterpret_cast<const uint4*>(base + (cb / S) * step_u + (cb % S) * step_v);
+    uint4 ra[F / 8], rb[F / 8];
+#pragma unroll
+    for (int blk = 0; blk < F / 8; ++blk) {
+      ra[blk] = pa[blk];
+      rb[blk] = pb[blk];
+    }
+    const __half2 sc = score_rows_f16<F>(q2, ra, rb);
+    if (__hgt(__low2half(sc), max_score)) {
+      max_score = __low2half(sc);
+      best = c;
+    }
+    if (c + 1 < NC && __hgt(__high2half(sc), max_score)) {
+      max_score = __high2half(sc);
+      best = c + 1;
+    }
+  }
+}
+
+// R > 0: radius known at compile time (interior levels take level_in_tile); R == 0: any radius.
+template <int F, int R>
+__global__ void __launch_bounds__(kTileThreads, 1)
+refine_f16_tile_kernel(const __half* __restrict__ D11, const __half* __restrict__ D21,
+                       const int64_t* __restrict__ p1, int64_t* __restrict__ p1_new,
+                       __half* __restrict__ scores, int H, int W, int radius, int dil_max,
+                       int cap_px) {
+  extern __shared__ __align__(128) unsigned char tile[];
+  __shared__ uint64_t bar;
+  __shared__ int box[4];  // min u, max u, min v, max v of the centres that can reach the image
+  const int tid = threadIdx.x;
+  const int x = blockIdx.x * kTilePatchW + (tid & (kTilePatchW - 1));
+  const int y = blockIdx.y * kTilePatchH + (tid / kTilePatchW);
+  const size_t b = blockIdx.z;
+  const bool active = x < W && y < H;
+  const size_t t = b * (size_t)H * W + (size_t)y * W + x;
+  const __half* __restrict__ img = D11 + b * (size_t)H * W * F;
+  const int halo = radius * dil_max;
+
+  if (tid == 0) {
+    box[0] = INT_MAX; box[1] = INT_MIN; box[2] = INT_MAX; box[3] = INT_MIN;
+    ptx::mbar_init(&bar, 1);
+    ptx::mbar_fence_init();
+  }
+  longlong2 p = make_longlong2(0, 0);
+  if (active) p = __ldg(reinterpret_cast<const longlong2*>(p1) + t);
+  // A centre further than the first-level reach from the image never sees an in-bounds
+  // candidate (the centre only moves onto in-bounds candidates), so it keeps p and score 0.
+  const bool reach = active && p.x >= -(long long)halo && p.x < (long long)W + halo &&
+                     p.y >= -(long long)halo && p.y < (long long)H + halo;
+  int u0 = reach ? (int)p.x : 0, v0 = reach ? (int)p.y : 0;
+  __syncthreads();
+  {
+    int mnu = reach ? u0 : INT_MAX, mxu = reach ? u0 : INT_MIN;
+    int mnv = reach ? v0 : INT_MAX, mxv = reach ? v0 : INT_MIN;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mnu = min(mnu, __shfl_xor_sync(0xffffffffu, mnu, o));
+      mxu = max(mxu, __shfl_xor_sync(0xffffffffu, mxu, o));
+      mnv = min(mnv, __shfl_xor_sync(0xffffffffu, mnv, o));
+      mxv = max(mxv, __shfl_xor_sync(0xffffffffu, mxv, o));
+    }
+    if ((tid & 31) == 0 && mnu <= mxu) {
+      atomicMin(&box[0], mnu); atomicMax(&box[1], mxu);
+      atomicMin(&box[2], mnv); atomicMax(&box[3], mxv);
+    }
+  }
+  __syncthreads();
+  // Row pitch of the staged box: a multiple of 8 pixels, so that pixels one row apart share a
+  // bank group only at equal u -- lanes of a quarter warp (consecutive u, rows differing by at
+  // most one for near-identity warps) then never collide (simulated 1.01 vs 1.12 wavefronts).
+  int tu0 = 0, tv0 = 0, TW = 0, TH = 0, pitch = 8;
+  if (box[0] <= box[1]) {
+    tu0 = max(box[0] - halo, 0);
+    tv0 = max(box[2] - halo, 0);
+    TW = min(box[1] + halo, W - 1) - tu0 + 1;
+    TH = min(box[3] + halo, H - 1) - tv0 + 1;
+    if (TW > (cap_px & ~7)) TW = cap_px & ~7;  // pathological spread: the rest reads global memory
+    pitch = (TW + 7) & ~7;
+    if (pitch * TH > cap_px) {
+      const int keep = cap_px / pitch;
+      tv0 += (TH - keep) / 2;
+      TH = keep;
+    }
+  }
+  if (tid < 32 && TH > 0) {
+    const uint32_t row_bytes = (uint32_t)TW * (F * 2);
+    if (tid == 0) ptx::mbar_arrive_expect_tx(&bar, row_bytes * (uint32_t)TH);
+    __syncwarp();
+    for (int r = tid; r < TH; r += 32)
+      ptx::bulk_g2s(tile + (size_t)r * pitch * (F * 2), img + ((size_t)(tv0 + r) * W + tu0) * F,
+                    row_bytes, &bar);
+  }
+
+  __half2 q2[F / 2];
+  if (reach) {
+    const uint4* qp = reinterpret_cast<const uint4*>(D21 + t * F);
+#pragma unroll
+    for (int blk = 0; blk < F / 8; ++blk) {
+      const uint4 xq = __ldg(qp + blk);
+      q2[blk * 4 + 0] = *reinterpret_cast<const __half2*>(&xq.x);
+      q2[blk * 4 + 1] = *reinterpret_cast<const __half2*>(&xq.y);
+      q2[blk * 4 + 2] = *reinterpret_cast<const __half2*>(&xq.z);
+      q2[blk * 4 + 3] = *reinterpret_cast<const __half2*>(&xq.w);
+    }
+  } else {
+#pragma unroll
+    for (int m = 0; m < F / 2; ++m) q2[m] = __float2half2_rn(0.0f);
+  }
+  if (TH > 0) ptx::mbar_wait(&bar, 0);
+
+  __half max_score = __float2half_rn(0.0f);
+  if (reach) {
+    const int side = 2 * radius + 1;
+    const int ncand = side * side;
+    for (int d = dil_max; d > 0; --d) {
+      const int ub = u0 - radius * d, vb = v0 - radius * d;
+      const int span = 2 * radius * d;
+      const int ru = ub - tu0, rv = vb - tv0;
+      if (R > 0 && ru >= 0 && ru + span < TW && rv >= 0 && rv + span < TH) {
+        int best = -1;
+        level_in_tile<F, (R > 0 ? R : 1)>(q2, tile + (size_t)(rv * pitch + ru) * (F * 2),
+                                          d * (F * 2), d * pitch * (F * 2), max_score, best);
+        if (best >= 0) {
+          constexpr int S = 2 * (R > 0 ? R : 1) + 1;
+          u0 = ub + (best / S) * d;
+          v0 = vb + (best % S) * d;
+        }
+        continue;
+      }
+      // border / out-of-tile level: per-candidate bounds tests, global-memory fallback
+      int u_new = u0, v_new = v0;
+      int i = 0, j = 0;  // candidate c = i * side + j  ->  (ub + i*d, vb + j*d)
+      for (int c = 0; c < ncand; c += 2) {
+        int cu[2], cv[2];
+        bool in[2];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          cu[k] = ub + i * d;
+          cv[k] = vb + j * d;
+          in[k] = c + k < ncand && cv[k] >= 0 && cv[k] < H && cu[k] >= 0 && cu[k] < W;
+          if (++j == side) { j = 0; ++i; }
+        }
+        if (!in[0] && !in[1]) continue;
+        // an out-of-image candidate borrows the address of the valid one; its score is ignored
+        uint4 ra[F / 8], rb[F / 8];
+        load_row_f16<F>(ra, tile, img, in[0] ? cu[0] : cu[1], in[0] ? cv[0] : cv[1], tu0, tv0, TW,
+                        TH, pitch, W);
+        load_row_f16<F>(rb, tile, img, in[1] ? cu[1] : cu[0], in[1] ? cv[1] : cv[0], tu0, tv0, TW,
+                        TH, pitch, W);
+        const __half2 s0 = score_rows_f16<F>(q2, ra, rb);
+        if (in[0] && __hgt(__low2half(s0), max_score)) {
+          max_score = __low2half(s0);
+          u_new = cu[0];
+          v_new = cv[0];
+        }
+        if (in[1] && __hgt(__high2half(s0), max_score)) {
+          max_score = __high2half(s0);
+          u_new = cu[1];
+          v_new = cv[1];
+        }
+      }
+      u0 = u_new;
+      v0 = v_new;
+    }
+  }
+  if (active) {
+    reinterpret_cast<longlong2*>(p1_new)[t] =
+        reach ? make_longlong2((long long)u0, (long long)v0) : p;
+    scores[t] = max_score;
+  }
+}
+
 // Generic-F fp16 path (scalar, any F).
 __global__ void __launch_bounds__(128)
 refine_f16_generic_kernel(const __half* __restrict__ D11, const __half* __restrict__ D21,
@@ -196,7 +436,29 @@ int launch_refine_f16(const __half* D11, const __half* D21, const int64_t* p1, i
   const bool aligned = ((reinterpret_cast<uintptr_t>(D11) | reinterpret_cast<uintptr_t>(D21) |
                          reinterpret_cast<uintptr_t>(p1) | reinterpret_cast<uintptr_t>(p1_new)) &
                         15) == 0;
-  if (F == 24 && aligned) {
+  if (aligned && N == H * W && (F == 24 || F == 16 || F == 32) && B <= 65535) {
+    dim3 tgrid((W + kTilePatchW - 1) / kTilePatchW, (H + kTilePatchH - 1) / kTilePatchH, B);
+    const int cap_px = kTileSmemBytes / (F * 2);
+#define FRODO_TILE_LAUNCH(FF, RR)                                                               \
+  do {                                                                                          \
+    static bool attr_set = false;                                                               \
+    if (!attr_set) {                                                                            \
+      FRODO_CUDA_TRY(cudaFuncSetAttribute(refine_f16_tile_kernel<FF, RR>,                       \
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize,          \
+                                          kTileSmemBytes));                                     \
+      attr_set = true;                                                                          \
+    }                                                                                           \
+    refine_f16_tile_kernel<FF, RR><<<tgrid, kTileThreads, kTileSmemBytes, s>>>(                 \
+        D11, D21, p1, p1_new, scores, H, W, radius, dil, cap_px);                               \
+  } while (0)
+    if (F == 24 && radius == 3) FRODO_TILE_LAUNCH(24, 3);
+    else if (F == 24) FRODO_TILE_LAUNCH(24, 0);
+    else if (F == 16 && radius == 3) FRODO_TILE_LAUNCH(16, 3);
+    else if (F == 16) FRODO_TILE_LAUNCH(16, 0);
+    else if (radius == 3) FRODO_TILE_LAUNCH(32, 3);
+    else FRODO_TILE_LAUNCH(32, 0);
+#undef FRODO_TILE_LAUNCH
+  } else if (F == 24 && aligned) {
     refine_f16_kernel<24><<<grid, 128, 0, s>>>(D11, D21, p1, p1_new, scores, H, W, N, radius, dil);
   } else if (F == 16 && aligned) {
     refine_f16_kernel<16><<<grid, 128, 0, s>>>(D11, D21, p1, p1_new, scores, H, W, N, radius, dil);
