@@ -566,28 +566,33 @@ gn_accumulate_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
 // 16-byte load per point instead of four 4-byte loads (4x fewer L1 requests and sectors:
 // the unpacked gather ran at ~23 sectors per warp request and kept the L1 tag stage busy
 // for the whole kernel, profiles/r1_ncu_accumulate.md).
-// Data movement per CTA (one edge, `pts_per_cta` points, tiles of 1024 points):
-//   * the streamed arrays of a tile (idx 8 KB, XC of frame j 16 KB, Q 4 KB, valid 1 KB:
+// Data movement per CTA (one edge, `pts_per_cta` points, tiles of 768 points):
+//   * the streamed arrays of a tile (idx 6 KB, XC of frame j 12 KB, Q 3 KB, valid 768 B:
 //     contiguous, read once) are fetched by the TMA unit (cp.async.bulk, SASS UBLKCP) into a
 //     3-stage shared-memory ring, one transaction mbarrier per stage;
-//   * lanes work on consecutive points (thread t: points t, t+256, t+512, t+768 of the
-//     tile), so a gather request covers 16 consecutive-ish sectors;
-//   * 4-slot gather ring refilled in place: right after point s of tile t is consumed, the
-//     gather of point s of tile t+1 is issued into the same registers, so every gather has
-//     a whole tile (~650 instructions x 4 warps per scheduler) to arrive;
+//   * lanes work on consecutive points (thread t: points t, t+256, t+512 of the tile), so a
+//     gather request covers 16 consecutive-ish sectors;
+//   * the gather of tile t+1 is issued at the start of tile t as asynchronous 16-byte copies
+//     global -> shared (cp.async, SASS LDGSTS) into a double-buffered gather area, one commit
+//     group per tile.  It needs no registers and no scoreboard: with the earlier in-register
+//     ring every refill shared a scoreboard with the loads still in flight, so each point
+//     waited for a gather issued a few instructions before (35 % of all stall samples,
+//     profiles/r1_ncu_accumulate.md v5 -> v6);
 //   * a stage is refilled with tile t+3 after the block-wide barrier that follows its last
 //     reader.
-// Requires N % 16 == 0, pts_per_cta % 1024 == 0 and 16-byte aligned XC, idx, Q, valid.
+// Requires N % 16 == 0, pts_per_cta % 768 == 0 and 16-byte aligned XC, idx, Q, valid.
 // ---------------------------------------------------------------------------
-constexpr int kTilePts = 1024;
+constexpr int kPtsPerThread = 3;
+constexpr int kTilePts = kPtsPerThread * kThreads;  // 768
 constexpr int kStages = 3;
-constexpr int kOffIdx = 0;                       // int64  [1024]
-constexpr int kOffXC = kOffIdx + kTilePts * 8;   // float4 [1024]  frame j (x,y,z,c)
-constexpr int kOffQ = kOffXC + kTilePts * 16;    // float  [1024]
-constexpr int kOffVm = kOffQ + kTilePts * 4;     // uint8  [1024]
+constexpr int kOffIdx = 0;                       // int64  [768]
+constexpr int kOffXC = kOffIdx + kTilePts * 8;   // float4 [768]   frame j (x,y,z,c)
+constexpr int kOffQ = kOffXC + kTilePts * 16;    // float  [768]
+constexpr int kOffVm = kOffQ + kTilePts * 4;     // uint8  [768]
 constexpr int kStageBytes = kOffVm + kTilePts;   // 29 bytes per point
 static_assert(kStageBytes % 128 == 0, "stage alignment");
-static_assert(kTilePts == 4 * kThreads, "the point loop is unrolled 4x per tile");
+constexpr int kGatherBytes = kTilePts * 16;    // float4 [768] frame i (x,y,z,c), x2 buffers
+constexpr int kRaysSmemBytes = kStages * kStageBytes + 2 * kGatherBytes;
 
 __global__ void pack_points_kernel(const float* __restrict__ Xs, const float* __restrict__ Cs,
                                    float4* __restrict__ XC, size_t total) {
@@ -679,26 +684,28 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
   __syncthreads();  // barriers initialised before anyone waits on them
 
   auto stage_of = [&](int t) { return stage_raw + (size_t)(t % kStages) * kStageBytes; };
-  auto tile_np = [&](int t) { return min(kTilePts, k_end - (k_begin + t * kTilePts)); };
-  // frame-i gather of point (t, s) of this thread (stage t must be full)
-  auto gather = [&](const unsigned char* st, int np, int s, float4& G) {
-    const int p = s * kThreads + tid;
-    if (p < np) {
-      long long ind = reinterpret_cast<const long long*>(st + kOffIdx)[p];
-      if (st[kOffVm + p] == 0) ind = 0;  // gn_kernels.cu:677
-      G = __ldg(XCi + ind);
-    }
+  auto gbuf_of = [&](int t) {
+    return reinterpret_cast<float4*>(stage_raw + (size_t)kStages * kStageBytes +
+                                     (size_t)(t & 1) * kGatherBytes);
   };
-  auto compute = [&](const unsigned char* st, int np, int s, const float4& G) {
-    const int p = s * kThreads + tid;
-    if (p < np) {
-      const float4 xj = reinterpret_cast<const float4*>(st + kOffXC)[p];
-      const float q = reinterpret_cast<const float*>(st + kOffQ)[p];
-      rays_point(c, A, G.x, G.y, G.z, xj.x, xj.y, xj.z, q, G.w, xj.w, st[kOffVm + p] != 0);
+  auto tile_np = [&](int t) { return min(kTilePts, k_end - (k_begin + t * kTilePts)); };
+  // frame-i gather of this thread's points of tile t (stage t must be full): async copies
+  auto issue_gather = [&](int t) {
+    const unsigned char* st = stage_of(t);
+    const int np = tile_np(t);
+    float4* gb = gbuf_of(t);
+#pragma unroll
+    for (int s = 0; s < kPtsPerThread; ++s) {
+      const int p = s * kThreads + tid;
+      if (p < np) {
+        long long ind = reinterpret_cast<const long long*>(st + kOffIdx)[p];
+        if (st[kOffVm + p] == 0) ind = 0;  // gn_kernels.cu:677
+        ptx::cp_async_16(gb + p, XCi + ind);
+      }
     }
+    ptx::cp_async_commit();
   };
 
-  float4 G[4];
   uint32_t phase_bits = 0;  // bit s = parity to wait for on stage s
   auto wait_stage = [&](int t) {
     const int s = t % kStages;
@@ -707,21 +714,28 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
   };
   if (ntile > 0) {
     wait_stage(0);
-    const unsigned char* st = stage_of(0);
-    const int np = tile_np(0);
-#pragma unroll
-    for (int s = 0; s < 4; ++s) gather(st, np, s, G[s]);
+    issue_gather(0);
   }
   for (int t = 0; t < ntile; ++t) {
-    const bool more = t + 1 < ntile;
-    if (more) wait_stage(t + 1);
+    if (t + 1 < ntile) {
+      wait_stage(t + 1);
+      issue_gather(t + 1);
+      ptx::cp_async_wait<1>();  // this thread's gathers of tile t have landed
+    } else {
+      ptx::cp_async_wait<0>();
+    }
     const unsigned char* st = stage_of(t);
-    const unsigned char* st1 = stage_of(t + 1);
-    const int np = tile_np(t), np1 = more ? tile_np(t + 1) : 0;
+    const float4* gb = gbuf_of(t);
+    const int np = tile_np(t);
 #pragma unroll
-    for (int s = 0; s < 4; ++s) {
-      compute(st, np, s, G[s]);
-      gather(st1, np1, s, G[s]);
+    for (int s = 0; s < kPtsPerThread; ++s) {
+      const int p = s * kThreads + tid;
+      if (p < np) {
+        const float4 G = gb[p];
+        const float4 xj = reinterpret_cast<const float4*>(st + kOffXC)[p];
+        const float q = reinterpret_cast<const float*>(st + kOffQ)[p];
+        rays_point(c, A, G.x, G.y, G.z, xj.x, xj.y, xj.z, q, G.w, xj.w, st[kOffVm + p] != 0);
+      }
     }
     __syncthreads();  // every reader of stage t % kStages is done
     if (tid == 0 && t + kStages < ntile) issue_tile(t + kStages);
@@ -734,18 +748,18 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
 }  // namespace
 
 // Points per accumulate CTA: minimises ceil(waves) * (points + fixed per-CTA cost) over a few
-// multiples of the 1024-point tile (2 CTAs per SM; the fixed cost ~ 1500 points covers the
+// multiples of the 768-point tile (2 CTAs per SM; the fixed cost ~ 1500 points covers the
 // pipeline fill and the reduction epilogue).
 int gn_pts_per_cta(int E, int N) {
-  const long long cand[] = {4096, 8192, 12288, 16384, 24576, 32768};
+  const long long cand[] = {3072, 6144, 9216, 12288, 18432, 24576, 36864};
   const double slots = 2.0 * kNumSMs;
-  long long best = 4096;
+  long long best = 3072;
   double best_cost = 1e300;
   for (long long ppc : cand) {
     const long long nch = ((long long)(N > 0 ? N : 1) + ppc - 1) / ppc;
     const double waves = (double)(nch * (long long)(E > 0 ? E : 1)) / slots;
     const double rounds = waves <= 1.0 ? 1.0 : (double)(long long)(waves + 0.999999);
-    const long long eff = ppc < N ? ppc : ((N + 1023) / 1024) * 1024;
+    const long long eff = ppc < N ? ppc : ((N + 767) / 768) * 768;
     const double cost = rounds * ((double)eff + 1500.0);
     if (cost < best_cost) {
       best_cost = cost;
@@ -781,7 +795,7 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
         reinterpret_cast<uintptr_t>(Q) | reinterpret_cast<uintptr_t>(valid)) & 15) == 0;
   if (prm.mode == FRODO_GN_RAYS && XC != nullptr && (N % 16) == 0 && aligned16) {
     static bool attr_set = false;
-    const size_t smem = (size_t)kStages * kStageBytes;
+    const size_t smem = (size_t)kRaysSmemBytes;
     if (!attr_set) {
       FRODO_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_rays_packed_kernel,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

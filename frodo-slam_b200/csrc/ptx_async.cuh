@@ -57,6 +57,19 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
       : "memory");
 }
 
+// Asynchronous 16-byte copy global -> shared (SASS LDGSTS), tracked by commit groups.
+__device__ __forceinline__ void cp_async_16(void* dst_smem, const void* src_gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src_gmem)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
 // Orders generic-proxy accesses (plain ld/st) against async-proxy accesses (bulk copies).
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async;" ::: "memory");
