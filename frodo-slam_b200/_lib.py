@@ -34,6 +34,7 @@ SIGNATURES = {
                                     c_void_p]),
     "frodo_gn_pack_points": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "frodo_gn_workspace_packed_offset": (c_size_t, [c_int, c_int, c_int]),
+    "frodo_gn_packed_bytes": (c_size_t, [c_int, c_int]),
     "frodo_gn_accumulate": (c_int, [ctypes.POINTER(GnParams)] + [c_void_p] * 10 + [c_int] * 4 +
                             [c_void_p] * 4 + [c_size_t, c_void_p]),
     "frodo_gn_solve_retract": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float,

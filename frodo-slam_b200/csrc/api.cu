@@ -41,8 +41,8 @@ size_t gn_carve_workspace(void* base, int K, int E, int N, GnWorkspace* ws) {
   const size_t o_tk = take(Ez * sizeof(int32_t));
   const size_t o_pt = take(Ez * max_chunks * kGnBlock * sizeof(float));
   const size_t o_eb = take(Ez * kGnBlock * sizeof(double));
-  // last: the pointmaps repacked as float4 (x,y,z,c), same size as Xs + Cs
-  const size_t o_pk = take((size_t)(K > 0 ? K : 1) * (size_t)(N > 0 ? N : 1) * 4 * sizeof(float));
+  // last: the pointmaps repacked in two layouts (frodo_gn_pack_points), ~32 bytes per point
+  const size_t o_pk = take(gn_packed_bytes(K, N));
   if (base != nullptr && ws != nullptr) {
     char* b = static_cast<char*>(base);
     ws->chol = reinterpret_cast<double*>(b + o_ch);
@@ -117,6 +117,8 @@ size_t frodo_gn_workspace_packed_offset(int K, int E, int N) {
   return ws.packed_off;
 }
 
+size_t frodo_gn_packed_bytes(int K, int N) { return gn_packed_bytes(K, N); }
+
 int frodo_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float* XC,
                          frodo_stream_t stream) {
   FRODO_ARG_CHECK(K >= 0 && N >= 0);
@@ -143,7 +145,7 @@ int frodo_gn_accumulate(const frodo_gn_params* params, const float* Twc, const f
   gn_carve_workspace(workspace, K, E, N, &ws);
   double* eb = edge_blocks ? edge_blocks : ws.edge_blocks;
   int rc = launch_gn_accumulate(*params, Twc, Xs, Cs, Kmat, XC, ii_row, jj_row, idx_ii2jj,
-                                valid_match, Q, N, E, ws.partials, ws.tickets, eb, done, s);
+                                valid_match, Q, K, N, E, ws.partials, ws.tickets, eb, done, s);
   if (rc) return rc;
   if (Hg == nullptr) return FRODO_OK;  // per-edge blocks only
   return launch_gn_assemble(eb, ii_row, jj_row, E, K, num_fix, Hg, done, s);

@@ -192,31 +192,10 @@ __device__ __forceinline__ void point_terms(const EdgeConst& c, float (&S)[28], 
 }
 
 // ---------------------------------------------------------------------------
-// rays, fast path.  The weighted outer products run on the packed fp32 pipe (FFMA2, two
-// fp32 lanes per issue slot).  A ray row a (a = 0,1,2) of the local Jacobian is
-//   x = [ d_a0 d_a1 d_a2 | c_a ],  d = (I - r r^T)/|P|,  c_a = row a of -[r]x
-// and c_a has exactly two non-zeros (+-r_p, +-r_q).  With the residual e_a appended it is
-// packed into three register pairs without padding:
-//   T0 = (d_a0, d_a1)   T1 = (d_a2, e_a)   M = (r_p, r_q)   (signs applied at unpack)
-// and adds, with W* = w * pair:
-//   TT  = W0.x*T0, W0.y*T0          -> S00 S01 (S10) S11        shared by all rows
-//   TU  = W0.x*T1, W0.y*T1          -> S02 v0 S12 v1             shared
-//   UU  = W1.x*T1                   -> S22 v2                    shared
-//   TM  = W0.x*M, W0.y*M            -> S0p S0q S1p S1q           per row
-//   UM  = W1.x*M, W1.y*M            -> S2p S2q vp vq             per row
-//   MM  = WM.x*M, WM.y*M            -> Spp Spq (Sqp) Sqq         per row
-// i.e. 11 FFMA2 + 3 FMUL2 per row.  The distance row [r0 r1 r2 | nj | e3] uses the same
-// T0/T1 accumulators with T0 = (r0,r1), T1 = (r2,e3) plus the nj column.
+// rays, fast path helpers (the kernel and its arithmetic are documented further down).
 // Weights: w = huber(|e| sqrt(q)/sigma) q/sigma^2 = min(1, 1.345 rsqrt(t)) wq with
 // t = wq e^2, wq = q/sigma^2 (same value as gn_kernels.cu:214-217,730-741, no sqrt(q)).
 // ---------------------------------------------------------------------------
-struct RaysAcc {
-  float2 TTa, TTb, TUa, TUb, UU;  // shared T-block accumulators
-  float2 TMa[3], TMb[3], UMa[3], UMb[3], MMa[3], MMb[3];  // per ray row
-  float2 N6a, N6b;  // (S06, S16), (S26, v6)
-  float n66;
-};
-
 __device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
 __device__ __forceinline__ float2 bc(float a) { return make_float2(a, a); }
 
@@ -226,128 +205,13 @@ __device__ __forceinline__ float rsqrt_fast(float x) {
   return y;
 }
 
-__device__ __forceinline__ float huber_w(float wq, float e) {
-  // min(1, 1.345 / (|e| sqrt(wq))) * wq ; wq = 0 -> 0
-  const float t = wq * e * e;
-  return fminf(1.0f, 1.345f * rsqrt_fast(t)) * wq;
-}
-
-__device__ __forceinline__ void t_block(RaysAcc& A, float2 W0, float2 W1, float2 T0, float2 T1) {
-  A.TTa = __ffma2_rn(bc(W0.x), T0, A.TTa);
-  A.TTb = __ffma2_rn(bc(W0.y), T0, A.TTb);
-  A.TUa = __ffma2_rn(bc(W0.x), T1, A.TUa);
-  A.TUb = __ffma2_rn(bc(W0.y), T1, A.TUb);
-  A.UU = __ffma2_rn(bc(W1.x), T1, A.UU);
-}
-
-template <int ROW>
-__device__ __forceinline__ void rays_row(RaysAcc& A, float w, float2 T0, float2 T1, float2 M) {
-  const float2 W0 = __fmul2_rn(bc(w), T0);
-  const float2 W1 = __fmul2_rn(bc(w), T1);
-  const float2 WM = __fmul2_rn(bc(w), M);
-  t_block(A, W0, W1, T0, T1);
-  A.TMa[ROW] = __ffma2_rn(bc(W0.x), M, A.TMa[ROW]);
-  A.TMb[ROW] = __ffma2_rn(bc(W0.y), M, A.TMb[ROW]);
-  A.UMa[ROW] = __ffma2_rn(bc(W1.x), M, A.UMa[ROW]);
-  A.UMb[ROW] = __ffma2_rn(bc(W1.y), M, A.UMb[ROW]);
-  A.MMa[ROW] = __ffma2_rn(bc(WM.x), M, A.MMa[ROW]);
-  A.MMb[ROW] = __ffma2_rn(bc(WM.y), M, A.MMb[ROW]);
-}
-
 struct RaysConst {
   float M[9];  // s_ij R(q_ij)
   float t[3];
   float sa2, sb2, C_thresh, Q_thresh;
 };
 
-__device__ __forceinline__ void rays_point(const RaysConst& c, RaysAcc& A, float xi0, float xi1,
-                                           float xi2, float xj0, float xj1, float xj2, float q,
-                                           float ci, float cj, bool vm) {
-  const float P0 = fmaf(c.M[0], xj0, fmaf(c.M[1], xj1, fmaf(c.M[2], xj2, c.t[0])));
-  const float P1 = fmaf(c.M[3], xj0, fmaf(c.M[4], xj1, fmaf(c.M[5], xj2, c.t[1])));
-  const float P2 = fmaf(c.M[6], xj0, fmaf(c.M[7], xj1, fmaf(c.M[8], xj2, c.t[2])));
-  const float n2j = fmaf(P0, P0, fmaf(P1, P1, P2 * P2));
-  const float a = rsqrt_fast(n2j);
-  const float nj = n2j * a;
-  const float r0 = P0 * a, r1 = P1 * a, r2 = P2 * a;
-  const float n2i = fmaf(xi0, xi0, fmaf(xi1, xi1, xi2 * xi2));
-  const float bi = rsqrt_fast(n2i);
-  const float ni = n2i * bi;
-  const float e0 = fmaf(-xi0, bi, r0);
-  const float e1 = fmaf(-xi1, bi, r1);
-  const float e2 = fmaf(-xi2, bi, r2);
-  const float e3 = nj - ni;
-  const bool valid = vm & (q > c.Q_thresh) & (ci > c.C_thresh) & (cj > c.C_thresh);
-  const float wq = valid ? q : 0.0f;
-  const float wr = c.sa2 * wq, wd = c.sb2 * wq;
-  const float w0 = huber_w(wr, e0), w1 = huber_w(wr, e1), w2 = huber_w(wr, e2);
-  const float w3 = huber_w(wd, e3);
-  // d r / d P = (I - r r^T) / |P|
-  const float s0 = -a * r0, s1 = -a * r1, s2 = -a * r2;
-  const float d00 = fmaf(s0, r0, a), d11 = fmaf(s1, r1, a), d22 = fmaf(s2, r2, a);
-  const float d01 = s0 * r1, d02 = s0 * r2, d12 = s1 * r2;
-  // c_0 = (0, r2, -r1)  c_1 = (-r2, 0, r0)  c_2 = (r1, -r0, 0): magnitudes only, signs at unpack
-  rays_row<0>(A, w0, f2(d00, d01), f2(d02, e0), f2(r1, r2));
-  rays_row<1>(A, w1, f2(d01, d11), f2(d12, e1), f2(r0, r2));
-  rays_row<2>(A, w2, f2(d02, d12), f2(d22, e2), f2(r0, r1));
-  // distance row [r0 r1 r2 | nj | e3]
-  {
-    const float2 T0 = f2(r0, r1), T1 = f2(r2, e3);
-    const float2 W0 = __fmul2_rn(bc(w3), T0), W1 = __fmul2_rn(bc(w3), T1);
-    t_block(A, W0, W1, T0, T1);
-    A.N6a = __ffma2_rn(W0, bc(nj), A.N6a);
-    A.N6b = __ffma2_rn(W1, bc(nj), A.N6b);
-    A.n66 = fmaf(w3 * nj, nj, A.n66);
-  }
-}
-
 __host__ __device__ constexpr int tri(int n, int m) { return n * 7 - n * (n - 1) / 2 + (m - n); }
-
-// Folds the packed accumulators into the canonical 28 upper-triangular entries + 7.
-// Row a's rotation entries sit at columns 3..5 with
-//   c_0: col 4 = +r2, col 5 = -r1 ; c_1: col 3 = -r2, col 5 = +r0 ; c_2: col 3 = +r1, col 4 = -r0
-// and the packed pairs hold M_0 = (r1, r2), M_1 = (r0, r2), M_2 = (r0, r1).
-__device__ __forceinline__ void rays_unpack(const RaysAcc& A, float (&S)[28], float (&v)[7]) {
-  S[tri(0, 0)] = A.TTa.x;
-  S[tri(0, 1)] = A.TTa.y;
-  S[tri(1, 1)] = A.TTb.y;
-  S[tri(0, 2)] = A.TUa.x;
-  S[tri(1, 2)] = A.TUb.x;
-  S[tri(2, 2)] = A.UU.x;
-  v[0] = A.TUa.y;
-  v[1] = A.TUb.y;
-  v[2] = A.UU.y;
-  // T x M: S[n][col]
-  //   row0: r1 -> col5 (-), r2 -> col4 (+) ; row1: r0 -> col5 (+), r2 -> col3 (-)
-  //   row2: r0 -> col4 (-), r1 -> col3 (+)
-  S[tri(0, 3)] = -A.TMa[1].y + A.TMa[2].y;
-  S[tri(0, 4)] = A.TMa[0].y - A.TMa[2].x;
-  S[tri(0, 5)] = -A.TMa[0].x + A.TMa[1].x;
-  S[tri(1, 3)] = -A.TMb[1].y + A.TMb[2].y;
-  S[tri(1, 4)] = A.TMb[0].y - A.TMb[2].x;
-  S[tri(1, 5)] = -A.TMb[0].x + A.TMb[1].x;
-  S[tri(2, 3)] = -A.UMa[1].y + A.UMa[2].y;
-  S[tri(2, 4)] = A.UMa[0].y - A.UMa[2].x;
-  S[tri(2, 5)] = -A.UMa[0].x + A.UMa[1].x;
-  v[3] = -A.UMb[1].y + A.UMb[2].y;
-  v[4] = A.UMb[0].y - A.UMb[2].x;
-  v[5] = -A.UMb[0].x + A.UMb[1].x;
-  // M x M
-  S[tri(3, 3)] = A.MMb[1].y + A.MMb[2].y;   // r2 r2 (row1) + r1 r1 (row2)
-  S[tri(4, 4)] = A.MMb[0].y + A.MMa[2].x;   // r2 r2 (row0) + r0 r0 (row2)
-  S[tri(5, 5)] = A.MMa[0].x + A.MMa[1].x;   // r1 r1 (row0) + r0 r0 (row1)
-  S[tri(3, 4)] = -A.MMa[2].y;               // row2: (+r1)(-r0)
-  S[tri(3, 5)] = -A.MMa[1].y;               // row1: (+r0)(-r2)
-  S[tri(4, 5)] = -A.MMa[0].y;               // row0: (-r1)(+r2)
-  S[tri(0, 6)] = A.N6a.x;
-  S[tri(1, 6)] = A.N6a.y;
-  S[tri(2, 6)] = A.N6b.x;
-  S[tri(3, 6)] = 0.f;
-  S[tri(4, 6)] = 0.f;
-  S[tri(5, 6)] = 0.f;
-  S[tri(6, 6)] = A.n66;
-  v[6] = A.N6b.y;
-}
 
 // Adjoint map M of pose i (7x7, fp64):  Jj = M x  (apply_Sim3_adj_inv, :319-339)
 __device__ void adjoint_matrix(const Sim3f& Ti, double* M /*[49]*/) {
@@ -560,52 +424,157 @@ gn_accumulate_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
 }
 
 // ---------------------------------------------------------------------------
-// rays fast path kernel: see the comment above RaysAcc for the arithmetic.
-// Inputs: the keyframe pointmaps repacked once per solve into XC [K][N] float4 (x,y,z,c)
-// (frodo_gn_pack_points), so that the data-dependent gather of frame i is ONE aligned
-// 16-byte load per point instead of four 4-byte loads (4x fewer L1 requests and sectors:
-// the unpacked gather ran at ~23 sectors per warp request and kept the L1 tag stage busy
-// for the whole kernel, profiles/r1_ncu_accumulate.md).
-// Data movement per CTA (one edge, `pts_per_cta` points, tiles of 768 points):
-//   * the streamed arrays of a tile (idx 6 KB, XC of frame j 12 KB, Q 3 KB, valid 768 B:
+// rays fast path kernel (v7): TWO points per thread in the two lanes of the packed fp32
+// instructions (FFMA2 / FMUL2 / FADD2): lane x = point p, lane y = point p + 256 of a
+// 512-point tile (so that the threads of a warp gather CONSECUTIVE points: two lanes then share
+// a 32-byte sector and the request is coalesced before it reaches L2 -- with lanes on points
+// 2k / 2k+1 every 16-byte gather was its own L2 sector request and the kernel ran into the L2
+// request rate, profiles/r1_ncu_accumulate.md).  Every
+// per-point quantity (transformed point, ray, residuals, Huber weights, Jacobian rows) and
+// every accumulator is a float2, so the whole per-point arithmetic runs at half the
+// instruction count of a scalar formulation and needs no pair-formation moves; the two lanes
+// of an accumulator are added once, after the last tile.
+// Inputs: the keyframe pointmaps repacked once per solve (frodo_gn_pack_points) in two layouts:
+//   XC [K][N]      float4 (x,y,z,c)                    -- target of the data-dependent gather
+//   XP [K][NB][256][8] (xA,xB,yA,yB,zA,zB,cA,cB)       -- streamed frame j, lanes pre-paired:
+//      block b = 512 consecutive points, A = point p, B = point p + 256 of the block
+//      (NB = ceil(N / 512), zero padded)
+// Data movement per CTA (one edge, `pts_per_cta` points, tiles of 512 points = one pair per
+// thread):
+//   * the streamed arrays of a tile (idx 4 KB, XP of frame j 8 KB, Q 2 KB, valid 512 B:
 //     contiguous, read once) are fetched by the TMA unit (cp.async.bulk, SASS UBLKCP) into a
-//     3-stage shared-memory ring, one transaction mbarrier per stage;
-//   * lanes work on consecutive points (thread t: points t, t+256, t+512 of the tile), so a
-//     gather request covers 16 consecutive-ish sectors;
-//   * the gather of tile t+1 is issued at the start of tile t as asynchronous 16-byte copies
-//     global -> shared (cp.async, SASS LDGSTS) into a double-buffered gather area, one commit
-//     group per tile.  It needs no registers and no scoreboard: with the earlier in-register
-//     ring every refill shared a scoreboard with the loads still in flight, so each point
-//     waited for a gather issued a few instructions before (35 % of all stall samples,
-//     profiles/r1_ncu_accumulate.md v5 -> v6);
-//   * a stage is refilled with tile t+3 after the block-wide barrier that follows its last
-//     reader.
-// Requires N % 16 == 0, pts_per_cta % 768 == 0 and 16-byte aligned XC, idx, Q, valid.
+//     kStages-deep shared-memory ring; a stage is handed back through an `empty` mbarrier on
+//     which every thread arrives right after it has read its operands, so there is no
+//     block-wide barrier in the loop;
+//   * the frame-i gather of tile t + kGatherDepth is issued at the start of tile t as
+//     asynchronous 16-byte copies global -> shared (cp.async, SASS LDGSTS), one commit group
+//     per tile: no registers, no scoreboard (the in-register ring of v5 made every point wait
+//     for a load issued a few instructions earlier, profiles/r1_ncu_accumulate.md).
+// Requires N % 16 == 0, pts_per_cta % 512 == 0 and 16-byte aligned XC, idx, Q, valid.
 // ---------------------------------------------------------------------------
-constexpr int kPtsPerThread = 3;
-constexpr int kTilePts = kPtsPerThread * kThreads;  // 768
-constexpr int kStages = 3;
-constexpr int kOffIdx = 0;                       // int64  [768]
-constexpr int kOffXC = kOffIdx + kTilePts * 8;   // float4 [768]   frame j (x,y,z,c)
-constexpr int kOffQ = kOffXC + kTilePts * 16;    // float  [768]
-constexpr int kOffVm = kOffQ + kTilePts * 4;     // uint8  [768]
+constexpr int kTilePts = 2 * kThreads;  // 512: one point pair per thread
+constexpr int kStages = 5;
+constexpr int kGatherDepth = 2;
+constexpr int kOffIdx = 0;                       // int64  [512]
+constexpr int kOffXP = kOffIdx + kTilePts * 8;   // float  [256][8] frame j, pair-interleaved
+constexpr int kOffQ = kOffXP + kTilePts * 16;    // float  [512]
+constexpr int kOffVm = kOffQ + kTilePts * 4;     // uint8  [512]
 constexpr int kStageBytes = kOffVm + kTilePts;   // 29 bytes per point
 static_assert(kStageBytes % 128 == 0, "stage alignment");
-constexpr int kGatherBytes = kTilePts * 16;    // float4 [768] frame i (x,y,z,c), x2 buffers
-constexpr int kRaysSmemBytes = kStages * kStageBytes + 2 * kGatherBytes;
+constexpr int kGatherBytes = kTilePts * 16;      // float4 [512] frame i (x,y,z,c)
+constexpr int kRaysSmemBytes = kStages * kStageBytes + (kGatherDepth + 1) * kGatherBytes;
 
+// XC (AoS float4) and XP (pair-interleaved per 512-point block) from Xs, Cs.  One thread per
+// pair slot (keyframe f, block b, pair p): points n = 512 b + p and n + 256.
 __global__ void pack_points_kernel(const float* __restrict__ Xs, const float* __restrict__ Cs,
-                                   float4* __restrict__ XC, size_t total) {
+                                   float4* __restrict__ XC, float4* __restrict__ XP, int K, int N,
+                                   int NB) {
+  const size_t slots = (size_t)K * NB * 256;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += stride) {
-    const float* x = Xs + p * 3;
-    XC[p] = make_float4(__ldg(x), __ldg(x + 1), __ldg(x + 2), __ldg(Cs + p));
+  for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < slots; k += stride) {
+    const int p = (int)(k & 255);
+    const size_t fb = k >> 8;
+    const int b = (int)(fb % NB);
+    const size_t f = fb / NB;
+    const int nA = b * 512 + p, nB = nA + 256;
+    float4 A = make_float4(0.f, 0.f, 0.f, 0.f), Bv = A;
+    if (nA < N) {
+      const float* x = Xs + (f * N + nA) * 3;
+      A = make_float4(__ldg(x), __ldg(x + 1), __ldg(x + 2), __ldg(Cs + f * N + nA));
+      XC[f * N + nA] = A;
+    }
+    if (nB < N) {
+      const float* x = Xs + (f * N + nB) * 3;
+      Bv = make_float4(__ldg(x), __ldg(x + 1), __ldg(x + 2), __ldg(Cs + f * N + nB));
+      XC[f * N + nB] = Bv;
+    }
+    XP[2 * k] = make_float4(A.x, Bv.x, A.y, Bv.y);
+    XP[2 * k + 1] = make_float4(A.z, Bv.z, A.w, Bv.w);
+  }
+}
+
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+
+// Huber weight of both lanes: min(1, 1.345 / (|e| sqrt(wq))) * wq ; wq = 0 -> 0.
+__device__ __forceinline__ float2 huber_w2(float2 wq, float2 e) {
+  const float2 t = mul2(mul2(wq, e), e);
+  float2 h = mul2(bc(1.345f), f2(rsqrt_fast(t.x), rsqrt_fast(t.y)));
+  h = f2(fminf(1.0f, h.x), fminf(1.0f, h.y));
+  return mul2(h, wq);
+}
+
+// S += w x x^T, v += w x e over the columns in MASK (both lanes).
+template <unsigned MASK>
+__device__ __forceinline__ void pair_row(float2 (&S)[28], float2 (&v)[7], const float2 (&x)[7],
+                                         float2 w, float2 e) {
+#pragma unroll
+  for (int m = 0; m < 7; ++m) {
+    if (!((MASK >> m) & 1u)) continue;
+    const float2 y = mul2(w, x[m]);
+    v[m] = fma2(y, e, v[m]);
+#pragma unroll
+    for (int n = m; n < 7; ++n) {
+      if (!((MASK >> n) & 1u)) continue;
+      S[tri(m, n)] = fma2(y, x[n], S[tri(m, n)]);
+    }
+  }
+}
+
+// Two points (lanes x, y).  Same quantities as rays_point; the rotation columns carry their
+// signs (c_0 = (0, r2, -r1), c_1 = (-r2, 0, r0), c_2 = (r1, -r0, 0)), so S and v are the
+// canonical upper-triangular entries directly.  A ray row a of the local Jacobian is
+//   x = [ d_a0 d_a1 d_a2 | c_a | 0 ],  d = (I - r r^T)/|P|,  c_a = row a of -[r]x,
+// the distance row is [ r0 r1 r2 | 0 0 0 | |P| ]; 74 FFMA2 + 19 FMUL2 per pair of points.
+__device__ __forceinline__ void rays_pair(const RaysConst& c, float2 (&S)[28], float2 (&v)[7],
+                                          const float4 xiA, const float4 xiB, float2 xj0,
+                                          float2 xj1, float2 xj2, float2 cj, float2 q, bool vmA,
+                                          bool vmB) {
+  const float2 P0 = fma2(bc(c.M[0]), xj0, fma2(bc(c.M[1]), xj1, fma2(bc(c.M[2]), xj2, bc(c.t[0]))));
+  const float2 P1 = fma2(bc(c.M[3]), xj0, fma2(bc(c.M[4]), xj1, fma2(bc(c.M[5]), xj2, bc(c.t[1]))));
+  const float2 P2 = fma2(bc(c.M[6]), xj0, fma2(bc(c.M[7]), xj1, fma2(bc(c.M[8]), xj2, bc(c.t[2]))));
+  const float2 n2j = fma2(P0, P0, fma2(P1, P1, mul2(P2, P2)));
+  const float2 a = f2(rsqrt_fast(n2j.x), rsqrt_fast(n2j.y));
+  const float2 nj = mul2(n2j, a);
+  const float2 r0 = mul2(P0, a), r1 = mul2(P1, a), r2 = mul2(P2, a);
+  const float2 xi0 = f2(xiA.x, xiB.x), xi1 = f2(xiA.y, xiB.y), xi2 = f2(xiA.z, xiB.z);
+  const float2 n2i = fma2(xi0, xi0, fma2(xi1, xi1, mul2(xi2, xi2)));
+  const float2 nbi = f2(-rsqrt_fast(n2i.x), -rsqrt_fast(n2i.y));
+  const float2 e0 = fma2(xi0, nbi, r0), e1 = fma2(xi1, nbi, r1), e2 = fma2(xi2, nbi, r2);
+  const float2 e3 = fma2(n2i, nbi, nj);  // |P| - |Xi|
+  const bool okA = vmA & (q.x > c.Q_thresh) & (xiA.w > c.C_thresh) & (cj.x > c.C_thresh);
+  const bool okB = vmB & (q.y > c.Q_thresh) & (xiB.w > c.C_thresh) & (cj.y > c.C_thresh);
+  const float2 wq = f2(okA ? q.x : 0.0f, okB ? q.y : 0.0f);
+  const float2 wr = mul2(bc(c.sa2), wq), wd = mul2(bc(c.sb2), wq);
+  const float2 w0 = huber_w2(wr, e0), w1 = huber_w2(wr, e1), w2 = huber_w2(wr, e2);
+  const float2 w3 = huber_w2(wd, e3);
+  // d r / d P = (I - r r^T) / |P| ; rotation columns -[r]x
+  const float2 na = mul2(a, bc(-1.0f));
+  const float2 s0 = mul2(na, r0), s1 = mul2(na, r1), s2 = mul2(na, r2);
+  const float2 d01 = mul2(s0, r1), d02 = mul2(s0, r2), d12 = mul2(s1, r2);
+  const float2 nr0 = mul2(r0, bc(-1.0f)), nr1 = mul2(r1, bc(-1.0f)), nr2 = mul2(r2, bc(-1.0f));
+  const float2 z = f2(0.f, 0.f);
+  {
+    const float2 x[7] = {fma2(s0, r0, a), d01, d02, z, r2, nr1, z};
+    pair_row<0x37u>(S, v, x, w0, e0);  // {0,1,2,4,5}
+  }
+  {
+    const float2 x[7] = {d01, fma2(s1, r1, a), d12, nr2, z, r0, z};
+    pair_row<0x2Fu>(S, v, x, w1, e1);  // {0,1,2,3,5}
+  }
+  {
+    const float2 x[7] = {d02, d12, fma2(s2, r2, a), r1, nr0, z, z};
+    pair_row<0x1Fu>(S, v, x, w2, e2);  // {0,1,2,3,4}
+  }
+  {
+    const float2 x[7] = {r0, r1, r2, z, z, z, nj};
+    pair_row<0x47u>(S, v, x, w3, e3);  // {0,1,2,6}
   }
 }
 
 __global__ void __launch_bounds__(kThreads, 2)
 gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
-                                 const float4* __restrict__ XC,
+                                 const float4* __restrict__ XC, const float4* __restrict__ XP,
                                  const int32_t* __restrict__ ii_row,
                                  const int32_t* __restrict__ jj_row,
                                  const int64_t* __restrict__ idx,
@@ -617,6 +586,7 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
   if (done != nullptr && *done != 0) return;
   extern __shared__ __align__(128) unsigned char stage_raw[];
   __shared__ __align__(8) uint64_t full_bar[kStages];
+  __shared__ __align__(8) uint64_t empty_bar[kStages];
   const int e = blockIdx.y;
   const int chunk = blockIdx.x;
   const int nchunks = gridDim.x;
@@ -626,7 +596,8 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
   const int k_end = min(N, k_begin + pts_per_cta);
   const int ntile = (k_end - k_begin + kTilePts - 1) / kTilePts;
   const float4* __restrict__ XCi = XC + (size_t)ix * N;
-  const float4* gXCj = XC + (size_t)jx * N;
+  const int NB = (N + kTilePts - 1) / kTilePts;
+  const float4* gXPj = XP + (size_t)jx * NB * kTilePts;  // padded to whole blocks
   const int64_t* gIdx = idx + (size_t)e * N;
   const uint8_t* gVm = valid_match + (size_t)e * N;
   const float* gQ = Q + (size_t)e * N;
@@ -637,14 +608,17 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
     const uint32_t np = (uint32_t)min(kTilePts, k_end - k0);
     unsigned char* st = stage_raw + (size_t)(t % kStages) * kStageBytes;
     uint64_t* bar = &full_bar[t % kStages];
-    ptx::mbar_arrive_expect_tx(bar, np * 29u);
+    ptx::mbar_arrive_expect_tx(bar, np * 13u + kTilePts * 16u);
     ptx::bulk_g2s(st + kOffIdx, gIdx + k0, np * 8u, bar);
-    ptx::bulk_g2s(st + kOffXC, gXCj + k0, np * 16u, bar);
+    ptx::bulk_g2s(st + kOffXP, gXPj + k0, kTilePts * 16u, bar);  // whole (padded) block
     ptx::bulk_g2s(st + kOffQ, gQ + k0, np * 4u, bar);
     ptx::bulk_g2s(st + kOffVm, gVm + k0, np, bar);
   };
   if (tid == 0) {
-    for (int s = 0; s < kStages; ++s) ptx::mbar_init(&full_bar[s], 1);
+    for (int s = 0; s < kStages; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], kThreads);
+    }
     ptx::mbar_fence_init();
     for (int t = 0; t < kStages && t < ntile; ++t) issue_tile(t);
   }
@@ -672,94 +646,120 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
     c.C_thresh = prm.C_thresh;
     c.Q_thresh = prm.Q_thresh;
   }
-  RaysAcc A;
-  {
-    const float2 z = make_float2(0.f, 0.f);
-    A.TTa = A.TTb = A.TUa = A.TUb = A.UU = A.N6a = A.N6b = z;
+  float2 S2[28], v2[7];
 #pragma unroll
-    for (int p = 0; p < 3; ++p)
-      A.TMa[p] = A.TMb[p] = A.UMa[p] = A.UMb[p] = A.MMa[p] = A.MMb[p] = z;
-    A.n66 = 0.f;
-  }
+  for (int k = 0; k < 28; ++k) S2[k] = f2(0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < 7; ++k) v2[k] = f2(0.f, 0.f);
   __syncthreads();  // barriers initialised before anyone waits on them
 
-  auto stage_of = [&](int t) { return stage_raw + (size_t)(t % kStages) * kStageBytes; };
-  auto gbuf_of = [&](int t) {
-    return reinterpret_cast<float4*>(stage_raw + (size_t)kStages * kStageBytes +
-                                     (size_t)(t & 1) * kGatherBytes);
-  };
-  auto tile_np = [&](int t) { return min(kTilePts, k_end - (k_begin + t * kTilePts)); };
-  // frame-i gather of this thread's points of tile t (stage t must be full): async copies
-  auto issue_gather = [&](int t) {
-    const unsigned char* st = stage_of(t);
-    const int np = tile_np(t);
-    float4* gb = gbuf_of(t);
-#pragma unroll
-    for (int s = 0; s < kPtsPerThread; ++s) {
-      const int p = s * kThreads + tid;
-      if (p < np) {
-        long long ind = reinterpret_cast<const long long*>(st + kOffIdx)[p];
-        if (st[kOffVm + p] == 0) ind = 0;  // gn_kernels.cu:677
-        ptx::cp_async_16(gb + p, XCi + ind);
+  // Ring positions advance by increment (no modulo in the loop); everything below is
+  // addressed through the shared window.
+  const uint32_t sm_base = ptx::smem_u32(stage_raw);
+  const uint32_t sm_gath = sm_base + kStages * kStageBytes + (uint32_t)tid * 32u;
+  const uint32_t sm_full = ptx::smem_u32(&full_bar[0]);
+  const uint32_t sm_empty = ptx::smem_u32(&empty_bar[0]);
+  const int npts = k_end - k_begin;
+  uint32_t full_phase = 0;  // bit s = parity to wait for on full_bar[s]
+  // Tile with `left` points from its start on, in stage sg, gather buffer gg: wait until the
+  // stage is full (every thread waits once per tile, here), then issue this thread's two
+  // frame-i gathers as async copies.
+  auto issue_gather = [&](int left, int sg, int gg) {
+    ptx::mbar_wait(sm_full + 8u * sg, (full_phase >> sg) & 1u);
+    full_phase ^= 1u << sg;
+    if (tid < left) {
+      const unsigned char* st = stage_raw + sg * kStageBytes;
+      const long long* ip = reinterpret_cast<const long long*>(st + kOffIdx);
+      const uint32_t dst = sm_gath + (uint32_t)gg * kGatherBytes;
+      long long ia = ip[tid];
+      if (st[kOffVm + tid] == 0) ia = 0;  // gn_kernels.cu:677
+      ptx::cp_async_16(dst, XCi + ia);
+      if (tid + kThreads < left) {
+        long long ib = ip[tid + kThreads];
+        if (st[kOffVm + tid + kThreads] == 0) ib = 0;
+        ptx::cp_async_16(dst + 16u, XCi + ib);
       }
     }
-    ptx::cp_async_commit();
   };
 
-  uint32_t phase_bits = 0;  // bit s = parity to wait for on stage s
-  auto wait_stage = [&](int t) {
-    const int s = t % kStages;
-    ptx::mbar_wait(&full_bar[s], (phase_bits >> s) & 1u);
-    phase_bits ^= 1u << s;
-  };
-  if (ntile > 0) {
-    wait_stage(0);
-    issue_gather(0);
-  }
-  for (int t = 0; t < ntile; ++t) {
-    if (t + 1 < ntile) {
-      wait_stage(t + 1);
-      issue_gather(t + 1);
-      ptx::cp_async_wait<1>();  // this thread's gathers of tile t have landed
-    } else {
-      ptx::cp_async_wait<0>();
-    }
-    const unsigned char* st = stage_of(t);
-    const float4* gb = gbuf_of(t);
-    const int np = tile_np(t);
 #pragma unroll
-    for (int s = 0; s < kPtsPerThread; ++s) {
-      const int p = s * kThreads + tid;
-      if (p < np) {
-        const float4 G = gb[p];
-        const float4 xj = reinterpret_cast<const float4*>(st + kOffXC)[p];
-        const float q = reinterpret_cast<const float*>(st + kOffQ)[p];
-        rays_point(c, A, G.x, G.y, G.z, xj.x, xj.y, xj.z, q, G.w, xj.w, st[kOffVm + p] != 0);
-      }
+  for (int g = 0; g < kGatherDepth; ++g) {
+    if (g < ntile) issue_gather(npts - g * kTilePts, g % kStages, g);
+    ptx::cp_async_commit();
+  }
+  uint32_t empty_phase = 0;          // producer only
+  int s_cur = 0, g_cur = 0;          // stage / gather buffer of tile t
+  int s_ahead = kGatherDepth % kStages, g_ahead = kGatherDepth;  // of tile t + kGatherDepth
+  int s_prev = kStages - 1;          // stage of tile t - 1
+  int left = npts;                   // points from the start of tile t to the end of the span
+  for (int t = 0; t < ntile; ++t) {
+    if (tid == 0 && t >= 1 && t - 1 + kStages < ntile) {
+      // every thread has read its operands of tile t-1: refill that stage
+      ptx::mbar_wait(sm_empty + 8u * s_prev, (empty_phase >> s_prev) & 1u);
+      empty_phase ^= 1u << s_prev;
+      issue_tile(t - 1 + kStages);
     }
-    __syncthreads();  // every reader of stage t % kStages is done
-    if (tid == 0 && t + kStages < ntile) issue_tile(t + kStages);
+    if (t + kGatherDepth < ntile) issue_gather(left - kGatherDepth * kTilePts, s_ahead, g_ahead);
+    ptx::cp_async_commit();
+    ptx::cp_async_wait<kGatherDepth>();  // this thread's gathers of tile t have landed
+    if (tid < left) {
+      const unsigned char* st = stage_raw + s_cur * kStageBytes;
+      float4 ja = reinterpret_cast<const float4*>(st + kOffXP)[2 * tid];
+      float4 jb = reinterpret_cast<const float4*>(st + kOffXP)[2 * tid + 1];
+      const float* qp = reinterpret_cast<const float*>(st + kOffQ);
+      const float4* gb = reinterpret_cast<const float4*>(
+          stage_raw + kStages * kStageBytes + g_cur * kGatherBytes) + 2 * tid;
+      const float4 xiA = gb[0];
+      float4 xiB;
+      float2 q;
+      bool vmA = st[kOffVm + tid] != 0, vmB;
+      if (tid + kThreads < left) {
+        xiB = gb[1];
+        q = f2(qp[tid], qp[tid + kThreads]);
+        vmB = st[kOffVm + tid + kThreads] != 0;
+      } else {  // ragged tail: lane y repeats lane x with zero weight
+        xiB = xiA;
+        q = f2(qp[tid], qp[tid]);
+        vmB = false;
+        ja = make_float4(ja.x, ja.x, ja.z, ja.z);
+        jb = make_float4(jb.x, jb.x, jb.z, jb.z);
+      }
+      ptx::mbar_arrive(sm_empty + 8u * s_cur);  // operands are in registers
+      rays_pair(c, S2, v2, xiA, xiB, f2(ja.x, ja.y), f2(ja.z, ja.w), f2(jb.x, jb.y),
+                f2(jb.z, jb.w), q, vmA, vmB);
+    } else {
+      ptx::mbar_arrive(sm_empty + 8u * s_cur);
+    }
+    s_prev = s_cur;
+    s_cur = s_cur + 1 == kStages ? 0 : s_cur + 1;
+    s_ahead = s_ahead + 1 == kStages ? 0 : s_ahead + 1;
+    g_cur = g_cur == kGatherDepth ? 0 : g_cur + 1;
+    g_ahead = g_ahead == kGatherDepth ? 0 : g_ahead + 1;
+    left -= kTilePts;
   }
   float S[28], v[7];
-  rays_unpack(A, S, v);
+#pragma unroll
+  for (int k = 0; k < 28; ++k) S[k] = S2[k].x + S2[k].y;
+#pragma unroll
+  for (int k = 0; k < 7; ++k) v[k] = v2[k].x + v2[k].y;
   edge_epilogue<kThreads>(S, v, Ti, e, chunk, nchunks, nchunks, partials, tickets, edge_blocks);
 }
 
 }  // namespace
 
 // Points per accumulate CTA: minimises ceil(waves) * (points + fixed per-CTA cost) over a few
-// multiples of the 768-point tile (2 CTAs per SM; the fixed cost ~ 1500 points covers the
+// multiples of the 512-point tile (2 CTAs per SM; the fixed cost ~ 1500 points covers the
 // pipeline fill and the reduction epilogue).
 int gn_pts_per_cta(int E, int N) {
-  const long long cand[] = {3072, 6144, 9216, 12288, 18432, 24576, 36864};
+  const long long cand[] = {2048, 4096, 6144, 8192, 12288, 16384, 24576, 32768};
   const double slots = 2.0 * kNumSMs;
-  long long best = 3072;
+  long long best = 2048;
   double best_cost = 1e300;
   for (long long ppc : cand) {
     const long long nch = ((long long)(N > 0 ? N : 1) + ppc - 1) / ppc;
     const double waves = (double)(nch * (long long)(E > 0 ? E : 1)) / slots;
     const double rounds = waves <= 1.0 ? 1.0 : (double)(long long)(waves + 0.999999);
-    const long long eff = ppc < N ? ppc : ((N + 767) / 768) * 768;
+    const long long eff = ppc < N ? ppc : ((N + 511) / 512) * 512;
     const double cost = rounds * ((double)eff + 1500.0);
     if (cost < best_cost) {
       best_cost = cost;
@@ -769,13 +769,22 @@ int gn_pts_per_cta(int E, int N) {
   return (int)best;
 }
 
+size_t gn_packed_bytes(int K, int N) {
+  const size_t k = (size_t)(K > 0 ? K : 1), n = (size_t)(N > 0 ? N : 1);
+  const size_t nb = (n + kTilePts - 1) / kTilePts;
+  return k * n * 16 + k * nb * kTilePts * 16;  // XC, then XP padded to whole blocks
+}
+
 int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float* XC,
                           cudaStream_t s) {
   const size_t total = (size_t)K * (size_t)N;
   if (total == 0) return FRODO_OK;
-  const int blocks = (int)((total + 255) / 256 < (size_t)(8 * kNumSMs) ? (total + 255) / 256
-                                                                       : (size_t)(8 * kNumSMs));
-  pack_points_kernel<<<blocks, 256, 0, s>>>(Xs, Cs, reinterpret_cast<float4*>(XC), total);
+  const int NB = (N + kTilePts - 1) / kTilePts;
+  const size_t slots = (size_t)K * NB * 256;
+  const size_t want = (slots + 255) / 256;
+  const int blocks = (int)(want < (size_t)(8 * kNumSMs) ? want : (size_t)(8 * kNumSMs));
+  float4* xc = reinterpret_cast<float4*>(XC);
+  pack_points_kernel<<<blocks, 256, 0, s>>>(Xs, Cs, xc, xc + total, K, N, NB);
   FRODO_CUDA_TRY(cudaGetLastError());
   return FRODO_OK;
 }
@@ -783,9 +792,9 @@ int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float*
 int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const float* Xs,
                          const float* Cs, const float* Kmat, const float* XC,
                          const int32_t* ii_row, const int32_t* jj_row, const int64_t* idx,
-                         const uint8_t* valid, const float* Q, int N, int E, float* partials,
-                         int32_t* tickets, double* edge_blocks, const int32_t* done,
-                         cudaStream_t s) {
+                         const uint8_t* valid, const float* Q, int K, int N, int E,
+                         float* partials, int32_t* tickets, double* edge_blocks,
+                         const int32_t* done, cudaStream_t s) {
   if (E == 0) return FRODO_OK;
   const int ppc = gn_pts_per_cta(E, N);
   const int nchunks = (N + ppc - 1) / ppc;
@@ -802,7 +811,8 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
       attr_set = true;
     }
     gn_accumulate_rays_packed_kernel<<<grid, kThreads, smem, s>>>(
-        prm, Twc, reinterpret_cast<const float4*>(XC), ii_row, jj_row, idx, valid, Q, N, ppc,
+        prm, Twc, reinterpret_cast<const float4*>(XC),
+        reinterpret_cast<const float4*>(XC) + (size_t)K * N, ii_row, jj_row, idx, valid, Q, N, ppc,
         partials, tickets, edge_blocks, done);
     FRODO_CUDA_TRY(cudaGetLastError());
     return FRODO_OK;

@@ -18,7 +18,7 @@ struct GnWorkspace {
   double* edge_blocks; // [E * 35]
   double* Hg;          // [(n+1) * n]
   double* chol;        // tile scratch of the cluster Cholesky (gn_chol_scratch_bytes)
-  float* packed;       // [K * N * 4] pointmaps as float4 (x,y,z,c), frodo_gn_pack_points
+  float* packed;       // [2 * K * N * 4]: XC float4 (x,y,z,c) then XP pair-interleaved
   size_t packed_off;   // byte offset of `packed` inside the workspace
   size_t bytes;
 };
@@ -27,14 +27,16 @@ size_t gn_carve_workspace(void* base, int K, int E, int N, GnWorkspace* ws);
 
 int launch_gn_edge_index(const int64_t* ii, const int64_t* jj, int E, int32_t* ii_row,
                          int32_t* jj_row, int32_t* n_unique, cudaStream_t s);
+// Bytes of the packed pointmap region (XC [K][N] float4 + XP padded to 512-point blocks).
+size_t gn_packed_bytes(int K, int N);
 int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float* XC,
                           cudaStream_t s);
-// XC: pointmaps packed by launch_gn_pack_points ([K][N] float4), or NULL.
+// XC: pointmaps packed by launch_gn_pack_points (XC [K][N] float4, then XP), or NULL.
 int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const float* Xs,
                          const float* Cs, const float* Kmat, const float* XC,
                          const int32_t* ii_row,
                          const int32_t* jj_row, const int64_t* idx, const uint8_t* valid,
-                         const float* Q, int N, int E, float* partials, int32_t* tickets,
+                         const float* Q, int K, int N, int E, float* partials, int32_t* tickets,
                          double* edge_blocks, const int32_t* done, cudaStream_t s);
 int launch_gn_assemble(const double* edge_blocks, const int32_t* ii_row, const int32_t* jj_row,
                        int E, int K, int num_fix, double* Hg, const int32_t* done, cudaStream_t s);

@@ -91,11 +91,15 @@ int frodo_gn_workspace_init(void* workspace, size_t workspace_bytes, int K, int 
                             frodo_stream_t stream);
 
 /* Rays fast path: repacks the keyframe pointmaps Xs [K,N,3] and confidences Cs [K,N] into
- * XC [K,N] float4 (x,y,z,c), 16-byte aligned, so that the data-dependent gather of
- * ray_align_kernel (gn_kernels.cu:677-681,714) is one aligned 16-byte load per point.  The
- * pointmaps do not change across Gauss-Newton iterations: pack once per solve and hand XC
- * to frodo_gn_accumulate.  frodo_gn_workspace_packed_offset gives the byte offset of a
- * K*N*16-byte region reserved for XC inside a workspace of frodo_gn_workspace_bytes. */
+ * XC, a 16-byte aligned region of frodo_gn_packed_bytes(K, N) bytes: first [K,N] float4
+ * (x,y,z,c), so that the data-dependent gather of ray_align_kernel
+ * (gn_kernels.cu:677-681,714) is one aligned 16-byte load per point, then the same data
+ * interleaved per point pair (xA,xB,yA,yB,zA,zB,cA,cB; A, B = points p, p+256 of a 512-point
+ * block, zero padded to whole blocks) for the streamed frame.  The pointmaps do not change
+ * across Gauss-Newton iterations: pack once per solve and hand XC to frodo_gn_accumulate.
+ * frodo_gn_workspace_packed_offset gives the byte offset of such a region inside a workspace
+ * of frodo_gn_workspace_bytes. */
+size_t frodo_gn_packed_bytes(int K, int N);
 int frodo_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float* XC,
                          frodo_stream_t stream);
 size_t frodo_gn_workspace_packed_offset(int K, int E, int N);
