@@ -11,7 +11,10 @@
 //                      rounded fp32 reciprocal (53 >= 2*24+2, Figueroa 1995);
 //   lambda *= 10.0   : exact product, single rounding.
 // Only  lambda *= 0.1  (0.1 is not an fp32 value) stays in fp64.
+#include <limits.h>
+
 #include "common.cuh"
+#include "ptx_async.cuh"
 
 namespace frodo {
 
@@ -136,12 +139,205 @@ iter_proj_kernel(const float* __restrict__ rays, const float* __restrict__ pts,
   converged[t] = conv ? 1 : 0;
 }
 
+// ---------------------------------------------------------------------------------------
+// Window-staged variant.  ncu on the kernel above: 31 sectors and 3.3 L1 wavefronts per
+// scalar texel load (the 36-byte AoS texel stride puts every lane in its own sector), 77.8 M
+// L1 wavefronts per 8 pairs = 93 % of its run time, top stall lg_throttle.  Shared memory
+// serves the same 4-byte loads at one wavefront per warp (lane stride 9 words is coprime
+// with the 32 banks).  A CTA owns a 32x16 patch of query pixels.  LM iteration 0 runs from
+// global memory (it moves the points from the initial guess to the neighbourhood of the
+// solution, mean 16 px on the synthetic pairs); then the bounding box of the patch's current
+// positions plus a margin is copied into shared memory with one cp.async.bulk per box row and
+// iterations 1.. fetch from there; a 2x2 footprint outside the box falls back to global
+// memory, so results never depend on the staging.  Arithmetic is shared with the kernel above.
+constexpr int kWinPatchW = 32, kWinPatchH = 16, kWinThreads = kWinPatchW * kWinPatchH;
+constexpr int kWinMargin = 4;
+constexpr int kWinSmemBytes = 108 * 1024;  // 2 CTAs per SM
+
+struct Lm {
+  float u, v, lambda;
+  bool conv;
+};
+
+// One LM iteration; texel(j, corner) returns channel j of corner 0..3 = (v11,u11), (v11,u11+1),
+// (v11+1,u11), (v11+1,u11+1) of the footprint selected by the last call of `locate`.
+template <typename Fetch>
+__device__ __forceinline__ void lm_iteration(Lm& s, float tx, float ty, float tz, float umax,
+                                             float vmax, float cost_thresh, Fetch&& fetch) {
+  const Weights w = bilinear_weights(s.u, s.v);
+  float c[9];
+  fetch(w.u11, w.v11, c, 9, w);
+  const float nrm = __fsqrt_rn(sum3(c[0], c[1], c[2], c[0], c[1], c[2]));
+  const float inv = __frcp_rn(nrm);
+  const float e0 = __fmaf_rn(c[0], inv, -tx);
+  const float e1 = __fmaf_rn(c[1], inv, -ty);
+  const float e2 = __fmaf_rn(c[2], inv, -tz);
+  const float cost = sum3(e0, e1, e2, e0, e1, e2);
+  float A00 = sum3(c[3], c[4], c[5], c[3], c[4], c[5]);
+  const float A01 = sum3(c[3], c[4], c[5], c[6], c[7], c[8]);
+  float A11 = sum3(c[6], c[7], c[8], c[6], c[7], c[8]);
+  const float egx = sum3(e0, e1, e2, c[3], c[4], c[5]);
+  const float egy = sum3(e0, e1, e2, c[6], c[7], c[8]);
+  A00 = __fadd_rn(A00, s.lambda);
+  A11 = __fadd_rn(A11, s.lambda);
+  const float det = __fmaf_rn(A00, A11, -__fmul_rn(A01, A01));
+  const float det_inv = __frcp_rn(det);
+  const float num_u = __fmaf_rn(A01, egy, -__fmul_rn(egx, A11));
+  const float num_v = __fmaf_rn(A01, egx, -__fmul_rn(egy, A00));
+  const float u_new = clampf(__fmaf_rn(num_u, det_inv, s.u), 1.0f, umax);
+  const float v_new = clampf(__fmaf_rn(num_v, det_inv, s.v), 1.0f, vmax);
+
+  const Weights q = bilinear_weights(u_new, v_new);
+  float d[9];
+  fetch(q.u11, q.v11, d, 3, q);
+  const float nrm2 = __fsqrt_rn(sum3(d[0], d[1], d[2], d[0], d[1], d[2]));
+  const float inv2 = __frcp_rn(nrm2);
+  const float f0 = __fmaf_rn(d[0], inv2, -tx);
+  const float f1 = __fmaf_rn(d[1], inv2, -ty);
+  const float f2 = __fmaf_rn(d[2], inv2, -tz);
+  const float new_cost = sum3(f0, f1, f2, f0, f1, f2);
+  if (new_cost < cost) {
+    s.u = u_new;
+    s.v = v_new;
+    s.lambda = __double2float_rn(__dmul_rn((double)s.lambda, 0.1));
+    s.conv = new_cost < cost_thresh;
+  } else {
+    s.lambda = __fmul_rn(s.lambda, 10.0f);
+    s.conv = cost < cost_thresh;
+  }
+}
+
+__global__ void __launch_bounds__(kWinThreads, 2)
+iter_proj_window_kernel(const float* __restrict__ rays, const float* __restrict__ pts,
+                        const float* __restrict__ p_init, float* __restrict__ p_new,
+                        uint8_t* __restrict__ converged, int H, int W, int max_iter,
+                        float lambda_init, float cost_thresh) {
+  extern __shared__ __align__(128) float win[];
+  __shared__ uint64_t bar;
+  __shared__ int box[4];
+  const int tid = threadIdx.x;
+  const int x = blockIdx.x * kWinPatchW + (tid & (kWinPatchW - 1));
+  const int y = blockIdx.y * kWinPatchH + (tid / kWinPatchW);
+  const size_t b = blockIdx.z;
+  const bool active = x < W && y < H;
+  const float* __restrict__ img = rays + b * (size_t)H * W * 9;
+  const size_t t = b * (size_t)H * W + (size_t)y * W + x;
+  if (tid == 0) {
+    box[0] = INT_MAX; box[1] = INT_MIN; box[2] = INT_MAX; box[3] = INT_MIN;
+    ptx::mbar_init(&bar, 1);
+    ptx::mbar_fence_init();
+  }
+  float tx = 0.f, ty = 0.f, tz = 0.f;
+  const float umax = (float)(W - 2), vmax = (float)(H - 2);
+  Lm s = {1.0f, 1.0f, lambda_init, false};
+  if (active) {
+    tx = __ldg(pts + t * 3 + 0);
+    ty = __ldg(pts + t * 3 + 1);
+    tz = __ldg(pts + t * 3 + 2);
+    const float2 p0 = __ldg(reinterpret_cast<const float2*>(p_init) + t);
+    s.u = clampf(p0.x, 1.0f, umax);
+    s.v = clampf(p0.y, 1.0f, vmax);
+  }
+  auto fetch_global = [&](int u11, int v11, float* c, int nch, const Weights& w) {
+    const float* r22 = img + ((size_t)v11 * W + u11) * 9;
+    const float* r12 = r22 + (size_t)W * 9;
+#pragma unroll
+    for (int j = 0; j < 9; ++j)
+      if (j < nch)
+        c[j] = blend(w.w11, __ldg(r12 + 9 + j), w.w12, __ldg(r12 + j), w.w21, __ldg(r22 + 9 + j),
+                     w.w22, __ldg(r22 + j));
+  };
+  if (active && max_iter > 0) lm_iteration(s, tx, ty, tz, umax, vmax, cost_thresh, fetch_global);
+  __syncthreads();  // box / barrier initialised
+  if (max_iter > 1) {
+    int mnu = INT_MAX, mxu = INT_MIN, mnv = INT_MAX, mxv = INT_MIN;
+    if (active) {
+      mnu = mxu = __float2int_rd(s.u);
+      mnv = mxv = __float2int_rd(s.v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mnu = min(mnu, __shfl_xor_sync(0xffffffffu, mnu, o));
+      mxu = max(mxu, __shfl_xor_sync(0xffffffffu, mxu, o));
+      mnv = min(mnv, __shfl_xor_sync(0xffffffffu, mnv, o));
+      mxv = max(mxv, __shfl_xor_sync(0xffffffffu, mxv, o));
+    }
+    if ((tid & 31) == 0 && mnu <= mxu) {
+      atomicMin(&box[0], mnu); atomicMax(&box[1], mxu);
+      atomicMin(&box[2], mnv); atomicMax(&box[3], mxv);
+    }
+  }
+  __syncthreads();
+  int tu0 = 0, tv0 = 0, TW = 0, TH = 0;
+  if (max_iter > 1 && box[0] <= box[1]) {
+    constexpr int cap = kWinSmemBytes / 36;  // texels
+    tu0 = max(box[0] - kWinMargin, 0) & ~3;                  // 16-byte aligned row starts
+    const int tu1 = min(box[1] + 1 + kWinMargin, W - 1);     // +1: right texel of the footprint
+    tv0 = max(box[2] - kWinMargin, 0);
+    const int tv1 = min(box[3] + 1 + kWinMargin, H - 1);
+    TW = (tu1 - tu0 + 1 + 3) & ~3;
+    if (tu0 + TW > W) TW = W - tu0;  // W % 4 == 0 keeps this a multiple of 4
+    TH = tv1 - tv0 + 1;
+    if (TW > (cap & ~3)) TW = cap & ~3;
+    if (TW * TH > cap) {
+      const int keep = cap / TW;
+      tv0 += (TH - keep) / 2;
+      TH = keep;
+    }
+    if (tid < 32) {
+      const uint32_t row_bytes = (uint32_t)TW * 36u;
+      if (tid == 0) ptx::mbar_arrive_expect_tx(&bar, row_bytes * (uint32_t)TH);
+      __syncwarp();
+      for (int r = tid; r < TH; r += 32)
+        ptx::bulk_g2s(win + (size_t)r * TW * 9, img + ((size_t)(tv0 + r) * W + tu0) * 9, row_bytes,
+                      &bar);
+    }
+    ptx::mbar_wait(&bar, 0);
+  }
+  if (active) {
+    auto fetch_window = [&](int u11, int v11, float* c, int nch, const Weights& w) {
+      const int ru = u11 - tu0, rv = v11 - tv0;
+      if (ru >= 0 && ru + 1 < TW && rv >= 0 && rv + 1 < TH) {
+        const float* r22 = win + (rv * TW + ru) * 9;
+        const float* r12 = r22 + TW * 9;
+#pragma unroll
+        for (int j = 0; j < 9; ++j)
+          if (j < nch)
+            c[j] = blend(w.w11, r12[9 + j], w.w12, r12[j], w.w21, r22[9 + j], w.w22, r22[j]);
+      } else {
+        fetch_global(u11, v11, c, nch, w);
+      }
+    };
+    for (int it = 1; it < max_iter; ++it)
+      lm_iteration(s, tx, ty, tz, umax, vmax, cost_thresh, fetch_window);
+    reinterpret_cast<float2*>(p_new)[t] = make_float2(s.u, s.v);
+    converged[t] = s.conv ? 1 : 0;
+  }
+}
+
 }  // namespace
 
 int launch_iter_proj(const float* rays, const float* pts, const float* p_init, float* p_new,
                      uint8_t* converged, int B, int H, int W, int N, int max_iter,
                      float lambda_init, float cost_thresh, cudaStream_t s) {
   if (B == 0 || N == 0) return FRODO_OK;
+  const bool aligned = (reinterpret_cast<uintptr_t>(rays) & 15) == 0 &&
+                       (reinterpret_cast<uintptr_t>(p_init) & 7) == 0 &&
+                       (reinterpret_cast<uintptr_t>(p_new) & 7) == 0;
+  if (N == H * W && (W % 4) == 0 && W >= 4 && H >= 3 && aligned && B <= 65535) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      FRODO_CUDA_TRY(cudaFuncSetAttribute(iter_proj_window_kernel,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          kWinSmemBytes));
+      attr_set = true;
+    }
+    dim3 wgrid((W + kWinPatchW - 1) / kWinPatchW, (H + kWinPatchH - 1) / kWinPatchH, B);
+    iter_proj_window_kernel<<<wgrid, kWinThreads, kWinSmemBytes, s>>>(
+        rays, pts, p_init, p_new, converged, H, W, max_iter, lambda_init, cost_thresh);
+    FRODO_CUDA_TRY(cudaGetLastError());
+    return FRODO_OK;
+  }
   dim3 grid((N + 127) / 128, B);
   iter_proj_kernel<<<grid, 128, 0, s>>>(rays, pts, p_init, p_new, converged, H, W, N, max_iter,
                                         lambda_init, cost_thresh);
