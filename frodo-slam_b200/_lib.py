@@ -41,6 +41,11 @@ SIGNATURES = {
                                        c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "frodo_gauss_newton": (c_int, [ctypes.POINTER(GnParams)] + [c_void_p] * 9 + [c_int] * 5 +
                            [c_float, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "frodo_gn_odom_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "frodo_gauss_newton_rays_odom": (c_int, [ctypes.POINTER(GnParams)] + [c_void_p] * 11 +
+                                     [c_int, c_int, c_void_p, c_float, c_float, c_float] +
+                                     [c_int] * 5 + [c_float, c_void_p, c_void_p, c_void_p,
+                                                    c_size_t, c_void_p]),
 }
 
 _lib = None

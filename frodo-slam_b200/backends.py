@@ -171,6 +171,47 @@ def gauss_newton_calib(Twc, Xs, Cs, K, ii, jj, idx_ii2jj, valid_match, Q, height
                          delta_thresh)
 
 
+def gauss_newton_rays_odom(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, odom_ii, odom_jj, Tij,
+                           s_bar, sigma_odom_t, sigma_odom_r, sigma_ray, sigma_dist,
+                           sigma_scale_prior, C_thresh, Q_thresh, num_fix, max_iter, delta_thresh):
+    """gn.cpp:29-62 / gn_kernels.cu:1792-1934: gauss_newton_rays + odometry constraints
+    (odom_ii -> odom_jj with measured relative poses Tij [Eo, 7|8]) + scale prior towards s_bar
+    [K] (host or device tensor, as the reference's caller passes it, global_opt.py:258).
+    Updates Twc in place, returns [dx]."""
+    dev, num_kf, N, E = _gn_validate(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, None)
+    _check_contiguous(odom_ii=odom_ii, odom_jj=odom_jj, Tij=Tij)
+    _check(odom_ii, "odom_ii", torch.int64, dev)
+    _check(odom_jj, "odom_jj", torch.int64, dev)
+    Eo = odom_ii.shape[0]
+    if odom_jj.shape[0] != Eo:
+        raise RuntimeError("odom_ii and odom_jj must have the same length")
+    stride = 0
+    if Eo > 0:
+        _check(Tij, "Tij", torch.float32, dev)
+        if Tij.dim() != 2 or Tij.shape[0] != Eo or Tij.shape[1] < 7:
+            raise RuntimeError("Tij must be [num_odom_edges, 7 or 8]")
+        stride = Tij.shape[1]
+    sb = torch.as_tensor(s_bar).to(device=dev, dtype=torch.float64).contiguous()
+    if sb.numel() != num_kf:
+        raise RuntimeError("s_bar must hold one scale target per keyframe")
+    p = GnParams(GN_RAYS, float(sigma_ray), float(sigma_dist), float(C_thresh), float(Q_thresh),
+                 0, 0, 0, 0.0)
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        dx = torch.zeros((max(num_kf - num_fix, 0), 7), dtype=torch.float32, device=dev)
+        if max_iter <= 0 or num_kf - num_fix <= 0:
+            return [dx]
+        nbytes = lib.frodo_gn_odom_workspace_bytes(num_kf, E, N, Eo)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        _lib.check(lib.frodo_gauss_newton_rays_odom(
+            ctypes.byref(p), _ptr(Twc), _ptr(Xs), _ptr(Cs), _ptr(ii), _ptr(jj), _ptr(idx_ii2jj),
+            _ptr(valid_match), _ptr(Q), _ptr(odom_ii), _ptr(odom_jj), _ptr(Tij) if Eo else None,
+            int(stride), int(Eo), _ptr(sb), float(sigma_odom_t), float(sigma_odom_r),
+            float(sigma_scale_prior), num_kf, N, E, int(num_fix), int(max_iter),
+            float(delta_thresh), _ptr(dx), None, _ptr(ws), nbytes, _stream()))
+    return [dx]
+
+
 def make_params(mode, **kw):
     """GnParams from keyword names of the reference ops (used by dist.py / tests / bench)."""
     if mode == "rays":

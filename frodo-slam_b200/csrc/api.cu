@@ -176,23 +176,37 @@ int frodo_gn_workspace_init(void* workspace, size_t workspace_bytes, int K, int 
   return FRODO_OK;
 }
 
-int frodo_gauss_newton(const frodo_gn_params* params, float* Twc, const float* Xs, const float* Cs,
-                       const float* Kmat, const int64_t* ii, const int64_t* jj,
-                       const int64_t* idx_ii2jj, const uint8_t* valid_match, const float* Q, int K,
-                       int N, int E, int num_fix, int max_iter, float delta_thresh, float* dx,
-                       int32_t* info, void* workspace, size_t workspace_bytes,
-                       frodo_stream_t stream) {
+// Shared driver of the single-call Gauss-Newton entry points.  `od` (may be NULL) adds the
+// odometry / scale-prior terms of gauss_newton_rays_odom; its scratch follows the base workspace.
+static int gn_run(const frodo_gn_params* params, float* Twc, const float* Xs, const float* Cs,
+                  const float* Kmat, const int64_t* ii, const int64_t* jj,
+                  const int64_t* idx_ii2jj, const uint8_t* valid_match, const float* Q, int K,
+                  int N, int E, int num_fix, int max_iter, float delta_thresh, float* dx,
+                  int32_t* info, void* workspace, size_t workspace_bytes, const GnOdom* od,
+                  frodo_stream_t stream) {
   FRODO_ARG_CHECK(params != nullptr && K >= 1 && N >= 0 && E >= 0 && num_fix >= 0 && num_fix <= K);
   FRODO_ARG_CHECK(workspace != nullptr);
-  FRODO_ARG_CHECK(workspace_bytes >= gn_carve_workspace(nullptr, K, E, N, nullptr));
+  const size_t base_bytes = gn_carve_workspace(nullptr, K, E, N, nullptr);
+  FRODO_ARG_CHECK(workspace_bytes >= base_bytes + (od ? gn_odom_scratch_bytes(od->Eo) : 0));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   GnWorkspace ws;
   gn_carve_workspace(workspace, K, E, N, &ws);
+  void* odom_scratch = static_cast<char*>(workspace) + base_bytes;  // base_bytes is 256-aligned
   int rc = frodo_gn_workspace_init(workspace, workspace_bytes, K, E, N, stream);
   if (rc) return rc;
   int32_t* done = ws.scalars + 1;
   int32_t* winfo = ws.scalars + 2;
-  rc = launch_gn_edge_index(ii, jj, E, ws.ii_row, ws.jj_row, ws.scalars, s);
+  if (od != nullptr && od->Eo > 0) {
+    // ranks of the odometry endpoints against the visual keyframe list: ii ranks, then jj ranks
+    int32_t* rows = static_cast<int32_t*>(odom_scratch);
+    rc = launch_gn_edge_index(ii, jj, E, ws.ii_row, ws.jj_row, ws.scalars, s, od->odom_ii, od->Eo,
+                              rows);
+    if (rc) return rc;
+    rc = launch_gn_edge_index(ii, jj, E, ws.ii_row, ws.jj_row, ws.scalars, s, od->odom_jj, od->Eo,
+                              rows + od->Eo);
+  } else {
+    rc = launch_gn_edge_index(ii, jj, E, ws.ii_row, ws.jj_row, ws.scalars, s);
+  }
   if (rc) return rc;
   // rays fast path: repack the pointmaps once per solve (they do not change across iterations)
   const float* XC = nullptr;
@@ -206,6 +220,10 @@ int frodo_gauss_newton(const frodo_gn_params* params, float* Twc, const float* X
                              valid_match, Q, K, N, E, num_fix, ws.Hg, ws.edge_blocks, done,
                              workspace, workspace_bytes, stream);
     if (rc) return rc;
+    if (od != nullptr) {
+      rc = launch_gn_add_odom(*od, Twc, K, num_fix, ws.Hg, done, odom_scratch, s);
+      if (rc) return rc;
+    }
     rc = launch_gn_solve_retract(ws.Hg, Twc, dx, K, num_fix, delta_thresh, done, winfo, ws.chol,
                                  s);
     if (rc) return rc;
@@ -213,6 +231,45 @@ int frodo_gauss_newton(const frodo_gn_params* params, float* Twc, const float* X
   if (info != nullptr)
     FRODO_CUDA_TRY(cudaMemcpyAsync(info, winfo, 2 * sizeof(int32_t), cudaMemcpyDeviceToDevice, s));
   return FRODO_OK;
+}
+
+int frodo_gauss_newton(const frodo_gn_params* params, float* Twc, const float* Xs, const float* Cs,
+                       const float* Kmat, const int64_t* ii, const int64_t* jj,
+                       const int64_t* idx_ii2jj, const uint8_t* valid_match, const float* Q, int K,
+                       int N, int E, int num_fix, int max_iter, float delta_thresh, float* dx,
+                       int32_t* info, void* workspace, size_t workspace_bytes,
+                       frodo_stream_t stream) {
+  return gn_run(params, Twc, Xs, Cs, Kmat, ii, jj, idx_ii2jj, valid_match, Q, K, N, E, num_fix,
+                max_iter, delta_thresh, dx, info, workspace, workspace_bytes, nullptr, stream);
+}
+
+size_t frodo_gn_odom_workspace_bytes(int K, int E, int N, int E_odom) {
+  return gn_carve_workspace(nullptr, K, E, N, nullptr) + gn_odom_scratch_bytes(E_odom);
+}
+
+int frodo_gauss_newton_rays_odom(const frodo_gn_params* params, float* Twc, const float* Xs,
+                                 const float* Cs, const int64_t* ii, const int64_t* jj,
+                                 const int64_t* idx_ii2jj, const uint8_t* valid_match,
+                                 const float* Q, const int64_t* odom_ii, const int64_t* odom_jj,
+                                 const float* Tij, int tij_stride, int E_odom, const double* s_bar,
+                                 float sigma_odom_t, float sigma_odom_r, float sigma_scale_prior,
+                                 int K, int N, int E, int num_fix, int max_iter,
+                                 float delta_thresh, float* dx, int32_t* info, void* workspace,
+                                 size_t workspace_bytes, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(params != nullptr && params->mode == FRODO_GN_RAYS);
+  FRODO_ARG_CHECK(E_odom >= 0 && (E_odom == 0 || (odom_ii && odom_jj && Tij && tij_stride >= 7)));
+  GnOdom od;
+  od.odom_ii = odom_ii;
+  od.odom_jj = odom_jj;
+  od.Tij = Tij;
+  od.stride = tij_stride;
+  od.Eo = E_odom;
+  od.s_bar = s_bar;
+  od.sigma_t = sigma_odom_t;
+  od.sigma_r = sigma_odom_r;
+  od.sigma_scale = sigma_scale_prior;
+  return gn_run(params, Twc, Xs, Cs, nullptr, ii, jj, idx_ii2jj, valid_match, Q, K, N, E, num_fix,
+                max_iter, delta_thresh, dx, info, workspace, workspace_bytes, &od, stream);
 }
 
 }  // extern "C"

@@ -15,7 +15,8 @@ __global__ void __launch_bounds__(kIdxThreads)
 edge_index_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int E, int P,
                   int64_t* __restrict__ keys_g, int32_t* __restrict__ pref_g,
                   int32_t* __restrict__ ii_row, int32_t* __restrict__ jj_row,
-                  int32_t* __restrict__ n_unique, int use_smem) {
+                  int32_t* __restrict__ n_unique, int use_smem,
+                  const int64_t* __restrict__ q_ids, int nq, int32_t* __restrict__ q_rows) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   int64_t* keys = use_smem ? reinterpret_cast<int64_t*>(smem_raw) : keys_g;
   int32_t* pref = use_smem ? reinterpret_cast<int32_t*>(smem_raw + (size_t)P * 8) : pref_g;
@@ -70,6 +71,18 @@ edge_index_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj
     }
     const int r = pref[lo];
     if (k < E) ii_row[k] = r; else jj_row[k - E] = r;
+  }
+  // extra queries (odometry edge endpoints): torch.searchsorted(unique, id), also for ids
+  // that are not keyframes of any visual edge (gn_kernels.cu:1817-1829)
+  const int total = scan[kIdxThreads - 1];
+  for (int k = tid; k < nq; k += kIdxThreads) {
+    const int64_t key = q_ids[k];
+    int lo = 0, hi = n2;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (keys[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    q_rows[k] = lo < n2 ? pref[lo] : total;
   }
 }
 
@@ -145,9 +158,11 @@ assemble_kernel(const double* __restrict__ edge_blocks, const int32_t* __restric
 }  // namespace
 
 int launch_gn_edge_index(const int64_t* ii, const int64_t* jj, int E, int32_t* ii_row,
-                         int32_t* jj_row, int32_t* n_unique, cudaStream_t s) {
+                         int32_t* jj_row, int32_t* n_unique, cudaStream_t s,
+                         const int64_t* q_ids, int nq, int32_t* q_rows) {
   if (E == 0) {
     if (n_unique) FRODO_CUDA_TRY(cudaMemsetAsync(n_unique, 0, sizeof(int32_t), s));
+    if (nq > 0) FRODO_CUDA_TRY(cudaMemsetAsync(q_rows, 0, (size_t)nq * sizeof(int32_t), s));
     return FRODO_OK;
   }
   int P = 2;
@@ -164,7 +179,7 @@ int launch_gn_edge_index(const int64_t* ii, const int64_t* jj, int E, int32_t* i
     attr_set = true;
   }
   edge_index_kernel<<<1, kIdxThreads, need, s>>>(ii, jj, E, P, nullptr, nullptr, ii_row, jj_row,
-                                                  n_unique, 1);
+                                                  n_unique, 1, q_ids, nq, q_rows);
   FRODO_CUDA_TRY(cudaGetLastError());
   return FRODO_OK;
 }

@@ -25,8 +25,25 @@ struct GnWorkspace {
 // Carves `base` (may be NULL to only compute sizes).  Returns total bytes.
 size_t gn_carve_workspace(void* base, int K, int E, int N, GnWorkspace* ws);
 
+// q_ids [nq] (optional): extra ids ranked against the same sorted unique list -> q_rows.
 int launch_gn_edge_index(const int64_t* ii, const int64_t* jj, int E, int32_t* ii_row,
-                         int32_t* jj_row, int32_t* n_unique, cudaStream_t s);
+                         int32_t* jj_row, int32_t* n_unique, cudaStream_t s,
+                         const int64_t* q_ids = nullptr, int nq = 0, int32_t* q_rows = nullptr);
+
+// gauss_newton_rays_odom extras (gn_odom.cu).  Scratch: [2*Eo] int32 rows (odom_ii ranks then
+// odom_jj ranks, written by launch_gn_edge_index) followed, 256-byte aligned, by [Eo][210] fp64.
+struct GnOdom {
+  const int64_t* odom_ii;  // [Eo] keyframe ids, used raw as Twc rows (gn_kernels.cu:1121-1122)
+  const int64_t* odom_jj;
+  const float* Tij;        // [Eo, stride]: t(3), q_xyzw(4)
+  int stride;
+  int Eo;
+  const double* s_bar;     // [K] device, may be NULL
+  float sigma_t, sigma_r, sigma_scale;
+};
+size_t gn_odom_scratch_bytes(int Eo);
+int launch_gn_add_odom(const GnOdom& od, const float* Twc, int K, int num_fix, double* Hg,
+                       const int32_t* done, void* scratch, cudaStream_t s);
 // Bytes of the packed pointmap region (XC [K][N] float4 + XP padded to 512-point blocks).
 size_t gn_packed_bytes(int K, int N);
 int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float* XC,

@@ -234,3 +234,50 @@ def keyframe_graph(num_kf, H, W, undirected, seed=1, device="cpu", pose_noise=0.
                 Xs=Xs, Cs=Cs.contiguous(), K=Kmat.float().to(device).contiguous(), ii=ii, jj=jj,
                 idx_ii2jj=idx.contiguous(), valid_match=valid.contiguous(), Q=Q.contiguous(),
                 H=H, W=W)
+
+
+# ----------------------------------------------------------------------- odometry edges
+
+ODOM_PARAMS = dict(sigma_odom_t=0.001, sigma_odom_r=0.001, sigma_ray=0.1,
+                   sigma_scale_prior=0.1)  # hard-coded by the caller, global_opt.py:253-257
+
+
+def _quat_mul(a, b):
+    """Hamilton product of [x,y,z,w] quaternions."""
+    ax, ay, az, aw = a.unbind(-1)
+    bx, by, bz, bw = b.unbind(-1)
+    return torch.stack([aw * bx + ax * bw + ay * bz - az * by,
+                        aw * by - ax * bz + ay * bw + az * bx,
+                        aw * bz + ax * by - ay * bx + az * bw,
+                        aw * bw - ax * bx - ay * by - az * bz], dim=-1)
+
+
+def odometry_edges(g, seed=7, noise_t=2e-4, noise_r=2e-4, skip_prior=(2,), device=None):
+    """Odometry inputs of gauss_newton_rays_odom for the keyframe graph `g` (keyframe_graph with
+    id_base=0, id_stride=1: the reference uses the ids as Twc rows, gn_kernels.cu:1121-1122):
+    edges k -> k+1 with measured relative pose [R_k^T R_{k+1}, R_k^T (t_{k+1} - t_k) / s_{k+1}]
+    of the TRUE poses (the prediction of gn_kernels.cu:1146-1155) plus small noise, and scale
+    targets s_bar = true scale (0 for the keyframes in `skip_prior`: skipped by the prior).
+    Returns dict(odom_ii, odom_jj [K-1] i64, Tij [K-1,8] f32, s_bar [K] f64 on the CPU)."""
+    T = g["Twc_true"].double().cpu()
+    K = T.shape[0]
+    gen = torch.Generator().manual_seed(seed)
+    i = torch.arange(0, K - 1)
+    j = i + 1
+    qi, qj = T[i, 3:7], T[j, 3:7]
+    qi_inv = qi * torch.tensor([-1.0, -1.0, -1.0, 1.0], dtype=torch.float64)
+    q_rel = _quat_mul(qi_inv, qj)
+    axis = torch.randn(K - 1, 3, generator=gen, dtype=torch.float64) * noise_r
+    dq = torch.cat([0.5 * axis, torch.ones(K - 1, 1, dtype=torch.float64)], dim=-1)
+    q_meas = _quat_mul(q_rel, dq)
+    q_meas = q_meas / q_meas.norm(dim=-1, keepdim=True)
+    Ri = quat_to_R(qi)
+    t_rel = torch.einsum("nji,nj->ni", Ri, T[j, 0:3] - T[i, 0:3]) / T[j, 7:8]
+    t_meas = t_rel + torch.randn(K - 1, 3, generator=gen, dtype=torch.float64) * noise_t
+    Tij = torch.cat([t_meas, q_meas, torch.ones(K - 1, 1, dtype=torch.float64)], dim=-1).float()
+    s_bar = T[:, 7].clone()
+    for k in skip_prior:
+        if k < K:
+            s_bar[k] = 0.0
+    dev = device if device is not None else g["Twc"].device
+    return dict(odom_ii=i.to(dev), odom_jj=j.to(dev), Tij=Tij.contiguous().to(dev), s_bar=s_bar)

@@ -152,6 +152,28 @@ int frodo_gauss_newton(const frodo_gn_params* params, float* Twc, const float* X
                        int32_t* info, void* workspace, size_t workspace_bytes,
                        frodo_stream_t stream);
 
+/* ---- gauss_newton_rays_odom: gn.cpp:29-62 / gn_kernels.cu:1792-1934 -----------------
+ * gauss_newton_rays plus, every iteration, relative-pose (odometry) constraints
+ * (odom_constraint_kernel_left_perturb_log, gn_kernels.cu:1106-1286) and a scale prior
+ * (apply_scale_prior_cpu, :1716-1790), added to the normal equations before the solve.
+ *   odom_ii, odom_jj [E_odom] int64: keyframe ids of edge i -> j.  As in the reference they
+ *     index the rows of Twc directly and are ranked against the keyframes of the visual
+ *     edges for the linear system.
+ *   Tij [E_odom, tij_stride] f32: measured relative pose (t(3), q_xyzw(4), ...), tij_stride >= 7.
+ *   s_bar [K] f64, device (the reference takes a host tensor; the Python operator uploads it):
+ *     scale targets, entries <= 1e-6 are skipped; NULL disables the prior.
+ * Workspace: frodo_gn_odom_workspace_bytes(K, E, N, E_odom) bytes. */
+size_t frodo_gn_odom_workspace_bytes(int K, int E, int N, int E_odom);
+int frodo_gauss_newton_rays_odom(const frodo_gn_params* params, float* Twc, const float* Xs,
+                                 const float* Cs, const int64_t* ii, const int64_t* jj,
+                                 const int64_t* idx_ii2jj, const uint8_t* valid_match,
+                                 const float* Q, const int64_t* odom_ii, const int64_t* odom_jj,
+                                 const float* Tij, int tij_stride, int E_odom, const double* s_bar,
+                                 float sigma_odom_t, float sigma_odom_r, float sigma_scale_prior,
+                                 int K, int N, int E, int num_fix, int max_iter,
+                                 float delta_thresh, float* dx, int32_t* info, void* workspace,
+                                 size_t workspace_bytes, frodo_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

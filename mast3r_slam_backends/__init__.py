@@ -13,6 +13,7 @@ from frodo_slam_b200.backends import (  # noqa: E402,F401
     gauss_newton_calib,
     gauss_newton_points,
     gauss_newton_rays,
+    gauss_newton_rays_odom,
     iter_proj,
     refine_matches,
 )

@@ -866,6 +866,199 @@ ORACLE_API int oracle_chol_solve(const double* H, const double* g, int n, double
  * [K-num_fix,7] receives the last iteration's update.  H_first/g_first (may be
  * NULL) receive the first iteration's assembled system (test aid).
  * Returns the number of iterations executed. */
+/* ------------------------------------------------------------------------------------------
+ * gauss_newton_rays_odom extras (gn_kernels.cu:1792-1934): odometry constraints
+ * (odom_constraint_kernel_left_perturb_log, :1106-1286, with its helpers quat_to_rot :562-574,
+ * vec_to_skew / R_to_vec / Jl_inv / logSE3 :1000-1086) restated in fp32, one odometry edge
+ * at a time, and the scale prior (apply_scale_prior_cpu, :1716-1790) in fp64.
+ * ------------------------------------------------------------------------------------------ */
+/* fp32 expressions below carry the FMA contractions nvcc 12.9 -O3 applies to the reference
+ * source (read from the SASS): a*b + c*d -> fma(a, b, round(c*d)); x +/- a*b -> fma; loops
+ * `acc += a*b` -> fma chains.  They matter: the rotation residual goes through
+ * acosf(0.5 (trace - 1)), which quantises angles below ~5e-4 rad, so one ulp in R_err can move
+ * the odometry residual by 3e-4 rad at an information of 1e6. */
+static void quat_to_rot_o(const float* q, float* R) { /* :562-574 */
+  const float qx = q[0], qy = q[1], qz = q[2], qw = q[3];
+  const float x2 = qx + qx, y2 = qy + qy, z2 = qz + qz;
+  const float wz = qw * z2, wy = qw * y2, wx = qw * x2;
+  const float ax = fmaf(-qx, x2, 1.0f), ay = fmaf(-qy, y2, 1.0f);
+  R[0] = fmaf(-qz, z2, ay);
+  R[1] = fmaf(qy, x2, -wz);
+  R[2] = fmaf(qz, x2, wy);
+  R[3] = fmaf(qy, x2, wz);
+  R[4] = fmaf(-qz, z2, ax);
+  R[5] = fmaf(qz, y2, -wx);
+  R[6] = fmaf(qz, x2, -wy);
+  R[7] = fmaf(qz, y2, wx);
+  R[8] = fmaf(-qy, y2, ax);
+}
+
+static void skew_o(const float* v, float* M) { /* :1000-1004 */
+  M[0] = 0;     M[1] = -v[2]; M[2] = v[1];
+  M[3] = v[2];  M[4] = 0;     M[5] = -v[0];
+  M[6] = -v[1]; M[7] = v[0];  M[8] = 0;
+}
+
+static void mat33_vec3(const float* A, const float* x, float* y) { /* :1088-1092 */
+  y[0] = fmaf(A[2], x[2], fmaf(A[0], x[0], A[1] * x[1]));
+  y[1] = fmaf(A[5], x[2], fmaf(A[3], x[0], A[4] * x[1]));
+  y[2] = fmaf(A[8], x[2], fmaf(A[6], x[0], A[7] * x[1]));
+}
+
+static void mat33_mat33(const float* A, const float* B, float* C) { /* :1095-1104 */
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) {
+      float acc = 0;
+      for (int k = 0; k < 3; ++k) acc = fmaf(A[r * 3 + k], B[k * 3 + c], acc);
+      C[r * 3 + c] = acc;
+    }
+}
+
+static void transpose33(const float* A, float* T) {
+  T[0] = A[0]; T[1] = A[3]; T[2] = A[6];
+  T[3] = A[1]; T[4] = A[4]; T[5] = A[7];
+  T[6] = A[2]; T[7] = A[5]; T[8] = A[8];
+}
+
+static void R_to_vec_o(const float* R, float* omega) { /* :1007-1041 */
+  const float trace = R[0] + R[4] + R[8];
+  float cos_angle = 0.5f * (trace - 1.0f);
+  cos_angle = fmaxf(-1.0f, fminf(1.0f, cos_angle));
+  const float angle = acosf(cos_angle);
+  if (fabsf(angle) < 1e-6f) {
+    omega[0] = omega[1] = omega[2] = 0.0f;
+  } else if (fabsf((float)(angle - M_PI)) < 1e-6f) { /* M_PI is a double: fp64 difference */
+    if (R[0] > R[4] && R[0] > R[8]) {
+      const float sv = 2.0f * sqrtf(R[0] - R[4] - R[8] + 1.0f);
+      omega[0] = 0.5f * sv; omega[1] = (R[3] + R[1]) / sv; omega[2] = (R[2] + R[6]) / sv;
+    } else if (R[4] > R[8]) {
+      const float sv = 2.0f * sqrtf(R[4] - R[0] - R[8] + 1.0f);
+      omega[0] = (R[3] + R[1]) / sv; omega[1] = 0.5f * sv; omega[2] = (R[7] + R[5]) / sv;
+    } else {
+      const float sv = 2.0f * sqrtf(R[8] - R[0] - R[4] + 1.0f);
+      omega[0] = (R[2] + R[6]) / sv; omega[1] = (R[7] + R[5]) / sv; omega[2] = 0.5f * sv;
+    }
+    omega[0] *= angle; omega[1] *= angle; omega[2] *= angle;
+  } else {
+    const float sin_angle = sinf(angle);
+    const float factor = angle / (2.0f * sin_angle);
+    omega[0] = factor * (R[7] - R[5]);
+    omega[1] = factor * (R[2] - R[6]);
+    omega[2] = factor * (R[3] - R[1]);
+  }
+}
+
+static void Jl_inv_o(const float* omega, float* J_inv) { /* :1044-1074 */
+  const float angle =
+      sqrtf(fmaf(omega[2], omega[2], fmaf(omega[0], omega[0], omega[1] * omega[1])));
+  float sk[9];
+  skew_o(omega, sk);
+  for (int i = 0; i < 9; ++i) J_inv[i] = (i % 4 == 0) ? 1.0f : 0.0f;
+  if (fabsf(angle) < 1e-6f) {
+    for (int i = 0; i < 9; ++i) J_inv[i] = fmaf(-0.5f, sk[i], J_inv[i]);
+  } else {
+    const float angle_sq = angle * angle;
+    const float sin_angle = sinf(angle), cos_angle = cosf(angle);
+    const float factor1 = -0.5f;
+    const float factor2 = (1.0f / angle_sq) - ((1.0f + cos_angle) / (2.0f * angle * sin_angle));
+    float sk2[9];
+    mat33_mat33(sk, sk, sk2);
+    for (int i = 0; i < 9; ++i) J_inv[i] += fmaf(factor1, sk[i], factor2 * sk2[i]);
+  }
+}
+
+/* Hs_odom [4,E,7,7], gs_odom [2,E,7] (fp32, reference layout).  odom_ii / odom_jj are used
+ * RAW as rows of Twc (:1121-1122); Tij rows hold [t(3), q_xyzw(4), ...] with `stride` floats. */
+ORACLE_API void oracle_odom_blocks(const float* Twc, const float* Tij, int stride,
+                                   const int64_t* odom_ii, const int64_t* odom_jj, int Eo,
+                                   float sigma_odom_t, float sigma_odom_r, float* Hs, float* gs) {
+  for (int idx = 0; idx < Eo; ++idx) {
+    const float* Ti = Twc + 8 * odom_ii[idx];
+    const float* Tj = Twc + 8 * odom_jj[idx];
+    const float *ti = Ti, *qi = Ti + 3, *tj = Tj, *qj = Tj + 3;
+    const float sj = Tj[7];
+    const float* tm = Tij + (size_t)stride * idx;
+    float R_m[9], R_i[9], R_j[9], R_i_T[9], R_j_T[9], R_m_T[9];
+    quat_to_rot_o(tm + 3, R_m);
+    quat_to_rot_o(qi, R_i);
+    quat_to_rot_o(qj, R_j);
+    transpose33(R_i, R_i_T);
+    transpose33(R_j, R_j_T);
+    transpose33(R_m, R_m_T);
+    float R_ij[9];
+    mat33_mat33(R_i_T, R_j, R_ij);
+    const float t_diff[3] = {tj[0] - ti[0], tj[1] - ti[1], tj[2] - ti[2]};
+    float R_iT_tdiff[3];
+    mat33_vec3(R_i_T, t_diff, R_iT_tdiff);
+    const float sj_inv = (sj == 0.0f) ? 1e6f : 1.0f / sj;
+    const float t_pred[3] = {sj_inv * R_iT_tdiff[0], sj_inv * R_iT_tdiff[1], sj_inv * R_iT_tdiff[2]};
+    float t_meas_inv[3];
+    mat33_vec3(R_m_T, tm, t_meas_inv);
+    t_meas_inv[0] *= -1.0f; t_meas_inv[1] *= -1.0f; t_meas_inv[2] *= -1.0f;
+    float R_err[9], Rm_T_tpred[3], t_err[3];
+    mat33_mat33(R_m_T, R_ij, R_err);
+    mat33_vec3(R_m_T, t_pred, Rm_T_tpred);
+    for (int k = 0; k < 3; ++k) t_err[k] = Rm_T_tpred[k] + t_meas_inv[k];
+    float r[6], J_inv[9];
+    R_to_vec_o(R_err, r + 3);
+    Jl_inv_o(r + 3, J_inv);
+    mat33_vec3(J_inv, t_err, r);
+    float Wd[6];
+    const float info_t = 1.0f / (sigma_odom_t * sigma_odom_t);
+    const float info_r = 1.0f / (sigma_odom_r * sigma_odom_r);
+    for (int k = 0; k < 3; ++k) Wd[k] = info_t * huber(r[k] / sigma_odom_t);
+    for (int k = 3; k < 6; ++k) Wd[k] = info_r * huber(r[k] / sigma_odom_r);
+    float J_i[42] = {0}, J_j[42] = {0};
+    float tj_inv[3], tj_sk[9], drho[9], drho_ds[3];
+    mat33_vec3(R_j_T, tj, tj_inv);
+    tj_inv[0] *= -1.0; tj_inv[1] *= -1.0; tj_inv[2] *= -1.0; /* fp64 literal, exact */
+    skew_o(tj_inv, tj_sk);
+    mat33_mat33(tj_sk, R_j_T, drho);
+    mat33_vec3(R_m_T, t_pred, drho_ds);
+    for (int rr = 0; rr < 3; ++rr) {
+      for (int c = 0; c < 3; ++c) {
+        J_j[rr * 7 + c] = R_j_T[rr * 3 + c];            /* d rho / d t_j */
+        J_j[rr * 7 + 3 + c] = drho[rr * 3 + c];         /* d rho / d theta_j */
+        J_j[(rr + 3) * 7 + 3 + c] = R_j_T[rr * 3 + c];  /* d phi / d theta_j */
+      }
+      J_j[rr * 7 + 6] = -drho_ds[rr];                   /* d rho / d s_j */
+    }
+    for (int k = 0; k < 42; ++k) J_i[k] = -J_j[k];
+    J_i[6] = J_i[13] = J_i[20] = 0.0f;
+    J_i[27] = J_i[34] = J_i[41] = 0.0f;
+    float J[84], JTW[84];
+    for (int rr = 0; rr < 6; ++rr)
+      for (int c = 0; c < 7; ++c) {
+        J[rr * 14 + c] = J_i[rr * 7 + c];
+        J[rr * 14 + 7 + c] = J_j[rr * 7 + c];
+      }
+    for (int a2 = 0; a2 < 14; ++a2)
+      for (int k = 0; k < 6; ++k) JTW[a2 * 6 + k] = J[k * 14 + a2] * Wd[k];
+    float Hf[196], gf[14];
+    for (int a2 = 0; a2 < 14; ++a2) {
+      for (int b2 = 0; b2 < 14; ++b2) {
+        float val = 0;
+        for (int k = 0; k < 6; ++k) val = fmaf(JTW[a2 * 6 + k], J[k * 14 + b2], val);
+        Hf[a2 * 14 + b2] = val;
+      }
+      float val = 0;
+      for (int k = 0; k < 6; ++k) val = fmaf(JTW[a2 * 6 + k], r[k], val);
+      gf[a2] = val;
+    }
+    for (int n2 = 0; n2 < 7; ++n2) {
+      gs[(0 * (size_t)Eo + idx) * 7 + n2] = gf[n2];
+      gs[(1 * (size_t)Eo + idx) * 7 + n2] = gf[n2 + 7];
+    }
+    for (int rr = 0; rr < 7; ++rr)
+      for (int c = 0; c < 7; ++c) {
+        Hs[((0 * (size_t)Eo + idx) * 7 + rr) * 7 + c] = Hf[rr * 14 + c];
+        Hs[((1 * (size_t)Eo + idx) * 7 + rr) * 7 + c] = Hf[rr * 14 + c + 7];
+        Hs[((2 * (size_t)Eo + idx) * 7 + rr) * 7 + c] = Hf[(rr + 7) * 14 + c];
+        Hs[((3 * (size_t)Eo + idx) * 7 + rr) * 7 + c] = Hf[(rr + 7) * 14 + c + 7];
+      }
+  }
+}
+
 ORACLE_API int oracle_gauss_newton(int mode, float* Twc, const float* Xs, const float* Cs,
                                    const float* Kmat, const int64_t* ii, const int64_t* jj,
                                    const int64_t* idx, const uint8_t* valid, const float* Q, int K,

@@ -196,3 +196,88 @@ def gauss_newton(mode, Twc, Xs, Cs, ii, jj, idx, valid, Q, sigma_a, sigma_b, C_t
         out["H"] = H
         out["g"] = g
     return out
+
+
+def odom_blocks(Twc, Tij, odom_ii, odom_jj, sigma_odom_t, sigma_odom_r):
+    """odom_constraint_kernel_left_perturb_log (gn_kernels.cu:1106-1286): Hs_odom [4,Eo,7,7],
+    gs_odom [2,Eo,7] in fp32.  odom_ii / odom_jj index Twc rows directly (:1121-1122)."""
+    Twc = _c(Twc, np.float32).reshape(-1, 8)
+    Tij = _c(Tij, np.float32)
+    Tij = Tij.reshape(Tij.shape[0], -1)
+    odom_ii = _c(odom_ii, np.int64)
+    odom_jj = _c(odom_jj, np.int64)
+    Eo = odom_ii.shape[0]
+    Hs = np.zeros((4, Eo, 7, 7), np.float32)
+    gs = np.zeros((2, Eo, 7), np.float32)
+    if Eo:
+        lib().oracle_odom_blocks(_p(Twc), _p(Tij), _c_i(Tij.shape[1]), _p(odom_ii), _p(odom_jj),
+                                 _c_i(Eo), _c_f(sigma_odom_t), _c_f(sigma_odom_r), _p(Hs), _p(gs))
+    return Hs, gs
+
+
+def add_blocks(H, g, Hs, gs, i_opt, j_opt):
+    """SparseBlock::update_lhs / update_rhs (gn_kernels.cu:72-122) for blocks [4,E,7,7] /
+    [2,E,7] with system block indices i_opt, j_opt (negative = fixed, skipped)."""
+    rows = [i_opt, i_opt, j_opt, j_opt]
+    cols = [i_opt, j_opt, i_opt, j_opt]
+    for b in range(4):
+        for e in range(Hs.shape[1]):
+            i, j = int(rows[b][e]), int(cols[b][e])
+            if i >= 0 and j >= 0:
+                H[7 * i:7 * i + 7, 7 * j:7 * j + 7] += Hs[b, e].astype(np.float64)
+    for b, ind in enumerate((i_opt, j_opt)):
+        for e in range(gs.shape[1]):
+            i = int(ind[e])
+            if i >= 0:
+                g[7 * i:7 * i + 7] += gs[b, e].astype(np.float64)
+
+
+def scale_prior(H, g, Twc, s_bar, num_fix, sigma_scale_prior):
+    """apply_scale_prior_cpu (gn_kernels.cu:1716-1790): residual log(s_i / sbar_i), J = 1."""
+    if sigma_scale_prior <= 1e-9:
+        return
+    info = 1.0 / (float(sigma_scale_prior) * float(sigma_scale_prior))
+    Twc64 = np.asarray(Twc, np.float32).reshape(-1, 8).astype(np.float64)
+    s_bar = np.asarray(s_bar, np.float64)
+    for i in range(num_fix, Twc64.shape[0]):
+        if s_bar[i] <= 1e-6 or Twc64[i, 6] <= 1e-6:  # sic: A.M - 1 = 6 indexes q_w, not s (:1736,1762)
+            continue
+        k = 7 * (i - num_fix) + 6
+        H[k, k] += info
+        g[k] += info * np.log(Twc64[i, 6] / s_bar[i])
+
+
+def gauss_newton_rays_odom(Twc, Xs, Cs, ii, jj, idx, valid, Q, odom_ii, odom_jj, Tij, s_bar,
+                           sigma_odom_t, sigma_odom_r, sigma_ray, sigma_dist, sigma_scale_prior,
+                           C_thresh, Q_thresh, num_fix, max_iter, delta_thresh):
+    """gauss_newton_rays_odom_cuda (gn_kernels.cu:1792-1934), composed from the pieces above.
+    Returns dict(Twc, dx, iters, fails)."""
+    Twc = np.array(Twc, dtype=np.float32, copy=True).reshape(-1, 8)
+    nK = np.asarray(Xs).shape[0]
+    ii = _c(ii, np.int64)
+    jj = _c(jj, np.int64)
+    odom_ii = _c(odom_ii, np.int64)
+    odom_jj = _c(odom_jj, np.int64)
+    ie, je, _ = edge_index(ii, jj)
+    uniq = np.unique(np.concatenate([ii, jj]))
+    oi_opt = np.searchsorted(uniq, odom_ii) - num_fix  # create_inds(unique, num_fix, odom_ii, ..)
+    oj_opt = np.searchsorted(uniq, odom_jj) - num_fix
+    n = 7 * (nK - num_fix)
+    dx = np.zeros((nK - num_fix, 7), np.float32)
+    iters = fails = 0
+    for _ in range(max_iter):
+        Hs, gs = edge_blocks("rays", Twc, Xs, Cs, ie, je, idx, valid, Q, sigma_ray, sigma_dist,
+                             C_thresh, Q_thresh)
+        H, g = assemble(Hs, gs, ie, je, nK, num_fix, round_f32=True)
+        if odom_ii.shape[0] > 0:
+            Ho, go = odom_blocks(Twc, Tij, odom_ii, odom_jj, sigma_odom_t, sigma_odom_r)
+            add_blocks(H, g, Ho, go, oi_opt, oj_opt)
+        scale_prior(H, g, Twc, s_bar, num_fix, sigma_scale_prior)
+        x, fail = chol_solve(H, g)
+        fails += int(fail)
+        dx = (-x).astype(np.float32).reshape(nK - num_fix, 7)
+        Twc = pose_retr(Twc, dx, num_fix)
+        iters += 1
+        if np.float32(np.sqrt(np.sum(dx.astype(np.float64) ** 2))) < delta_thresh:
+            break
+    return dict(Twc=Twc, dx=dx, iters=iters, fails=fails)

@@ -84,3 +84,33 @@ def expand_edge_blocks(eb):
     A[:, iu[1], iu[0]] = eb[:, :28]
     gj = eb[:, 28:]
     return np.stack([A, -A, -A, A]), np.stack([-gj, gj])
+
+
+OP = synth.ODOM_PARAMS
+
+
+def odom_inputs(g, **kw):
+    return synth.odometry_edges(g, **kw)
+
+
+def oracle_gn_odom(g, od, num_fix, max_iter, delta_thresh=0.0):
+    from oracle import oracle
+    return oracle.gauss_newton_rays_odom(
+        g["Twc"].numpy(), g["Xs"].numpy(), g["Cs"].numpy(), g["ii"].numpy(), g["jj"].numpy(),
+        g["idx_ii2jj"].numpy(), g["valid_match"].numpy(), g["Q"].numpy(), od["odom_ii"].numpy(),
+        od["odom_jj"].numpy(), od["Tij"].numpy(), od["s_bar"].numpy(), OP["sigma_odom_t"],
+        OP["sigma_odom_r"], OP["sigma_ray"], GP["sigma_dist"], OP["sigma_scale_prior"],
+        GP["C_conf"], GP["Q_conf"], num_fix, max_iter, delta_thresh)
+
+
+def backend_gn_odom(be, g, od, dev, num_fix, max_iter, delta_thresh=0.0):
+    """gauss_newton_rays_odom called as global_opt.py:260-283 does (s_bar stays a CPU tensor)."""
+    t = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in g.items()}
+    Twc = t["Twc"].clone()
+    dx = be.gauss_newton_rays_odom(
+        Twc, t["Xs"], t["Cs"], t["ii"], t["jj"], t["idx_ii2jj"], t["valid_match"], t["Q"],
+        od["odom_ii"].to(dev), od["odom_jj"].to(dev), od["Tij"].to(dev), od["s_bar"],
+        OP["sigma_odom_t"], OP["sigma_odom_r"], OP["sigma_ray"], GP["sigma_dist"],
+        OP["sigma_scale_prior"], GP["C_conf"], GP["Q_conf"], num_fix, max_iter, delta_thresh)
+    torch.cuda.synchronize()
+    return Twc.cpu().numpy(), dx[0].cpu().numpy()

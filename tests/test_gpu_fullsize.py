@@ -217,3 +217,51 @@ def test_fullsize_gn_system_and_solve_vs_oracle(be, dev):
     Twc, dx = backend_gn(be, "rays", g, dev, 1, 2)
     ref = oracle_gn("rays", g, 1, 2)
     assert rel_err(Twc, ref["Twc"]) < GN_TOL
+
+
+# ------------------------------------------ gauss_newton_rays_odom
+
+@pytest.mark.parametrize("cfg,num_fix,iters", [("window8", 1, 1), ("window8", 1, 3),
+                                               ("window8", 2, 2), ("calib32", 1, 2)])
+def test_gn_rays_odom_vs_oracle(be, dev, cfg, num_fix, iters):
+    from helpers import backend_gn_odom, odom_inputs, oracle_gn_odom
+    g = graph_inputs(cfg, 48, 64)
+    od = odom_inputs(g)
+    Twc, dx = backend_gn_odom(be, g, od, dev, num_fix, iters)
+    ref = oracle_gn_odom(g, od, num_fix, iters)
+    assert ref["fails"] == 0
+    assert rel_err(Twc, ref["Twc"]) < GN_TOL
+    if iters == 1:
+        assert rel_err(dx, ref["dx"]) < GN_TOL
+    assert np.array_equal(Twc[:num_fix], g["Twc"].numpy()[:num_fix])
+
+
+def test_gn_rays_odom_without_odometry_equals_rays_plus_prior(be, dev):
+    """No odometry edges and s_bar = 0 (every prior skipped) -> exactly gauss_newton_rays."""
+    from helpers import OP, backend_gn_odom
+    g = graph_inputs("window8", 48, 64)
+    od = dict(odom_ii=torch.zeros(0, dtype=torch.long), odom_jj=torch.zeros(0, dtype=torch.long),
+              Tij=torch.zeros(0, 8), s_bar=torch.zeros(8, dtype=torch.float64))
+    Ta, da = backend_gn_odom(be, g, od, dev, 1, 2)
+    t = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in g.items()}
+    Twc = t["Twc"].clone()
+    db = be.gauss_newton_rays(Twc, t["Xs"], t["Cs"], t["ii"], t["jj"], t["idx_ii2jj"],
+                              t["valid_match"], t["Q"], OP["sigma_ray"], GP["sigma_dist"],
+                              GP["C_conf"], GP["Q_conf"], 1, 2, 0.0)
+    torch.cuda.synchronize()
+    assert np.array_equal(Ta, Twc.cpu().numpy()) and np.array_equal(da, db[0].cpu().numpy())
+
+
+def test_gn_rays_odom_vs_reference(be, dev, ref_backend, capfd):
+    if ref_backend is None:
+        pytest.skip("oracle/_ref not built")
+    from helpers import backend_gn_odom, odom_inputs
+    g = graph_inputs("window8", 48, 64)
+    od = odom_inputs(g)
+    for num_fix, iters in ((1, 1), (1, 3), (2, 2)):
+        Ta, da = backend_gn_odom(be, g, od, dev, num_fix, iters)
+        Tb, db = backend_gn_odom(ref_backend, g, od, dev, num_fix, iters)
+        assert rel_err(Ta, Tb) < GN_TOL, (num_fix, iters)
+        if iters == 1:
+            assert rel_err(da, db) < GN_TOL
+    capfd.readouterr()

@@ -110,3 +110,28 @@ def test_gn_oracle_reduces_cost_and_honours_delta_thresh():
     e1 = np.abs(r["Twc"] - g["Twc_true"].numpy()).max()
     assert e1 < e0
     assert np.array_equal(r["Twc"][0], g["Twc"].numpy()[0])  # fixed pose untouched
+
+
+def test_odometry_blocks_structure():
+    """odom restatement: zero residual at a consistent measurement, symmetric PSD 14x14 block,
+    J_i = -J_j except for the scale column (gn_kernels.cu:1236-1241)."""
+    import pytest
+    from frodo_slam_b200 import synth
+    from helpers import OP
+    from oracle import oracle
+    g = graph_inputs("window8", 16, 16)
+    od = synth.odometry_edges(g, noise_t=0.0, noise_r=0.0)
+    Hs, gs = oracle.odom_blocks(g["Twc_true"].numpy(), od["Tij"].numpy(), od["odom_ii"].numpy(),
+                                od["odom_jj"].numpy(), OP["sigma_odom_t"], OP["sigma_odom_r"])
+    info = 1.0 / OP["sigma_odom_t"] ** 2
+    assert np.abs(gs).max() < 2e-3 * info  # residual ~ fp32 rounding of the relative pose
+    for e in range(Hs.shape[1]):
+        full = np.block([[Hs[0, e], Hs[1, e]], [Hs[2, e], Hs[3, e]]]).astype(np.float64)
+        assert np.allclose(full, full.T, rtol=1e-5, atol=1e-5 * info)
+        assert np.linalg.eigvalsh(0.5 * (full + full.T)).min() > -1e-4 * info
+        assert np.allclose(Hs[0, e][:6, :6], Hs[3, e][:6, :6], rtol=1e-5, atol=1e-6 * info)
+        assert np.all(Hs[0, e][6, :] == 0) and np.all(Hs[0, e][:, 6] == 0)
+    H = np.zeros((49, 49))
+    gv = np.zeros(49)
+    oracle.scale_prior(H, gv, g["Twc"].numpy(), od["s_bar"].numpy(), 1, 0.1)
+    assert np.count_nonzero(H) == 6 and H[6, 6] == pytest.approx(100.0)  # keyframe 2 skipped

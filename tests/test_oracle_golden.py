@@ -68,3 +68,26 @@ def test_gn_oracle_num_fix_2(gold):
     r = _gn(gold, "rays", 2, 2)
     assert rel_err(r["Twc"], gold["gn_rays_fix2_Twc"]) < 1e-4
     assert np.array_equal(r["Twc"][:2], gold["gn_Twc"][:2])  # pinned poses untouched
+
+
+# ------------------------------------------------ gauss_newton_rays_odom (golden_ref_odom.npz)
+
+GOLD_ODOM = os.path.join(os.path.dirname(__file__), "golden", "golden_ref_odom.npz")
+
+
+@pytest.mark.parametrize("num_fix,iters", [(1, 1), (1, 3), (2, 2)])
+def test_gn_rays_odom_oracle_matches_reference(num_fix, iters):
+    """Recorded from the unmodified reference by tests/golden/make_golden_ref_odom.py."""
+    from helpers import OP
+    from oracle import oracle
+    gd = np.load(GOLD_ODOM)
+    r = oracle.gauss_newton_rays_odom(
+        gd["gn_Twc"], gd["gn_Xs"], gd["gn_Cs"], gd["gn_ii"], gd["gn_jj"],
+        gd["gn_idx"].astype(np.int64), gd["gn_valid"], gd["gn_Q"], gd["odom_ii"], gd["odom_jj"],
+        gd["Tij"], gd["s_bar"], OP["sigma_odom_t"], OP["sigma_odom_r"], OP["sigma_ray"],
+        GP["sigma_dist"], OP["sigma_scale_prior"], GP["C_conf"], GP["Q_conf"], num_fix, iters, 0.0)
+    assert r["fails"] == 0 and r["iters"] == iters
+    assert rel_err(r["Twc"], gd[f"odom_fix{num_fix}_it{iters}_Twc"]) < 1e-4
+    if iters == 1:
+        assert rel_err(r["dx"], gd[f"odom_fix{num_fix}_it{iters}_dx"]) < 1e-4
+    assert np.array_equal(r["Twc"][:num_fix], gd["gn_Twc"][:num_fix])
