@@ -31,13 +31,14 @@ Twc = g["Twc"].clone()
 sg = fdist.ShardedGaussNewton(prm, Twc, g["Xs"], g["Cs"], None, g["ii"], g["jj"],
                               g["idx_ii2jj"].view(E, N), g["valid_match"].view(E, N),
                               g["Q"].view(E, N), 0, E, 1)
+n = 7 * (K - 1)
+T, Tc = (n + 1 + 31) // 32, (n + 31) // 32
+off = (T * (T + 1) // 2 * 1024 + 32) * 8
+sg.ws[off:off + 128 * 8].zero_()
 for _ in range(3):
     Twc.copy_(g["Twc"])
     sg.solve(1, 0.0)
 torch.cuda.synchronize()
-n = 7 * (K - 1)
-T, Tc = (n + 1 + 31) // 32, (n + 31) // 32
-off = (T * (T + 1) // 2 * 1024 + 32) * 8
 st = sg.ws[off:off + 128 * 8].view(torch.int64).cpu().numpy().astype("float64")
 mhz = 1965.0
 us = lambda a, b: (b - a) / mhz  # noqa: E731
@@ -55,3 +56,8 @@ for k in range(Tc):
 print({k: round(float(v), 2) for k, v in tot.items()})
 print(f"back substitution   {us(st[2 + 3 * Tc], st[3 + 3 * Tc]):8.2f} us")
 print(f"total               {us(st[0], st[3 + 3 * Tc]):8.2f} us")
+# cycles accumulated by every diagonal-tile call since the workspace was allocated (3 solves)
+if st[120] > 0:
+    calls = 3 * Tc
+    print(f"diagonal tile: factor {st[120] / mhz / calls:6.2f} us, inverse W {st[121] / mhz / calls:6.2f} us "
+          f"per tile (mean of {calls} calls)")

@@ -56,7 +56,7 @@ def test_argument_errors_without_gpu():
 
 def test_operator_surface_matches_reference_signatures():
     import mast3r_slam_backends as be
-    want = {  # gn.cpp:3-12, 63-74, 90-103, 120-126, 137-142 (positional order)
+    want = {  # gn.cpp:3-12, 29-45, 63-74, 90-103, 120-126, 137-142 (positional order)
         "iter_proj": ["rays_img_with_grad", "pts_3d_norm", "p_init", "max_iter", "lambda_init",
                       "cost_thresh"],
         "refine_matches": ["D11", "D21", "p1", "radius", "dilation_max"],
@@ -68,6 +68,11 @@ def test_operator_surface_matches_reference_signatures():
         "gauss_newton_calib": ["Twc", "Xs", "Cs", "K", "ii", "jj", "idx_ii2jj", "valid_match", "Q",
                                "height", "width", "pixel_border", "z_eps", "sigma_pixel",
                                "sigma_depth", "C_thresh", "Q_thresh", "max_iter", "delta_thresh"],
+        # gn.cpp:29-45 (its s_bar is named s_residuals in the binding, s_bar in the driver)
+        "gauss_newton_rays_odom": ["Twc", "Xs", "Cs", "ii", "jj", "idx_ii2jj", "valid_match", "Q",
+                                   "odom_ii", "odom_jj", "Tij", "s_bar", "sigma_odom_t",
+                                   "sigma_odom_r", "sigma_ray", "sigma_dist", "sigma_scale_prior",
+                                   "C_thresh", "Q_thresh", "num_fix", "max_iter", "delta_thresh"],
     }
     for name, args in want.items():
         assert list(inspect.signature(getattr(be, name)).parameters) == args, name
