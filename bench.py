@@ -258,7 +258,9 @@ def main_ours(args):
     prof = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof):
         try:
-            roofline["traffic"] = json.load(open(prof)).get("gn_accumulate_rays_bytes_per_launch")
+            full = json.load(open(prof)).get("gn_accumulate_rays_bytes_per_launch")
+            # measured on the full 256-edge launch; a rank's launch covers E_local edges
+            roofline["traffic"] = None if full is None else int(full * (hi - lo) / E)
         except Exception:
             pass
 
