@@ -243,7 +243,15 @@ __device__ void adjoint_matrix(const Sim3f& Ti, double* M /*[49]*/) {
 // per chunk; the last CTA of the edge (ticket) sums the chunks in fixed order in fp64 and
 // applies the adjoint: A = M S M^T, g = M v.
 // Slot (e, chunk) of `partials` is at (e * stride + chunk); stride >= nchunks.
-template <int THREADS>
+// BAR = 0: the whole CTA (THREADS == blockDim.x); otherwise named barrier BAR over the first
+// THREADS threads (the consumer warps of a warp-specialised CTA).
+template <int THREADS, int BAR>
+__device__ __forceinline__ void epi_sync() {
+  if constexpr (BAR == 0) __syncthreads();
+  else ptx::named_bar_sync<BAR, THREADS>();
+}
+
+template <int THREADS, int BAR = 0>
 __device__ __forceinline__ void edge_epilogue(float (&S)[28], float (&v)[7], const Sim3f& Ti,
                                               int e, int chunk, int nchunks, int stride,
                                               float* __restrict__ partials,
@@ -279,7 +287,7 @@ __device__ __forceinline__ void edge_epilogue(float (&S)[28], float (&v)[7], con
       if (lane == 0) warp_part[warp][28 + l] = x;
     }
   }
-  __syncthreads();
+  epi_sync<THREADS, BAR>();
   float* __restrict__ my_part = partials + ((size_t)e * stride + chunk) * kGnBlock;
   if (threadIdx.x < kGnBlock) {
     float x = 0.f;
@@ -288,12 +296,12 @@ __device__ __forceinline__ void edge_epilogue(float (&S)[28], float (&v)[7], con
     my_part[threadIdx.x] = x;
   }
   __threadfence();
-  __syncthreads();
+  epi_sync<THREADS, BAR>();
   if (threadIdx.x == 0) {
     const int t = atomicAdd(tickets + e, 1);
     is_last = (t == nchunks - 1);
   }
-  __syncthreads();
+  epi_sync<THREADS, BAR>();
   if (!is_last) return;
   __threadfence();
 
@@ -310,20 +318,20 @@ __device__ __forceinline__ void edge_epilogue(float (&S)[28], float (&v)[7], con
   }
   if (threadIdx.x == 64) adjoint_matrix(Ti, Md);
   if (threadIdx.x == 0) tickets[e] = 0;  // ready for the next iteration
-  __syncthreads();
+  epi_sync<THREADS, BAR>();
   if (threadIdx.x < 49) {
     const int r = threadIdx.x / 7, cc = threadIdx.x % 7;
     const int a = min(r, cc), b = max(r, cc);
     Sfull[threadIdx.x] = Sd[a * 7 - a * (a - 1) / 2 + (b - a)];
   }
-  __syncthreads();
+  epi_sync<THREADS, BAR>();
   if (threadIdx.x < 49) {
     const int r = threadIdx.x / 7, cc = threadIdx.x % 7;
     double acc = 0.0;
     for (int a = 0; a < 7; ++a) acc += Md[r * 7 + a] * Sfull[a * 7 + cc];
     MS[threadIdx.x] = acc;
   }
-  __syncthreads();
+  epi_sync<THREADS, BAR>();
   double* __restrict__ out = edge_blocks + (size_t)e * kGnBlock;
   if (threadIdx.x < 49) {
     const int r = threadIdx.x / 7, cc = threadIdx.x % 7;
@@ -452,7 +460,23 @@ gn_accumulate_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
 //     for a load issued a few instructions earlier, profiles/r1_ncu_accumulate.md).
 // Requires N % 16 == 0, pts_per_cta % 512 == 0 and 16-byte aligned XC, idx, Q, valid.
 // ---------------------------------------------------------------------------
-constexpr int kTilePts = 2 * kThreads;  // 512: one point pair per thread
+// FRODO_ABL: development switches for ablation builds (profiles/exp_ablation.py); 0 in the product
+#ifndef FRODO_ABL
+#define FRODO_ABL 0
+#endif
+#ifndef FRODO_RAYS_WS
+#define FRODO_RAYS_WS 0   // 1: warp-specialised persistent variant (gn_accumulate_ws.cuh), slower
+#endif
+#ifndef FRODO_RAYS_THREADS
+#if FRODO_RAYS_WS
+#define FRODO_RAYS_THREADS 512
+#else
+#define FRODO_RAYS_THREADS 128   // 4 CTAs x 128 threads per SM: 475 us; 2 x 256: 485 us
+#endif
+#endif
+constexpr int kRaysThreads = FRODO_RAYS_THREADS;        // threads per CTA of the rays kernel
+constexpr int kRaysCtasPerSM = 512 / kRaysThreads;      // 16 warps per SM either way
+constexpr int kTilePts = 2 * kRaysThreads;  // one point pair per thread
 constexpr int kStages = 5;
 constexpr int kGatherDepth = 2;
 constexpr int kOffIdx = 0;                       // int64  [512]
@@ -469,14 +493,14 @@ constexpr int kRaysSmemBytes = kStages * kStageBytes + (kGatherDepth + 1) * kGat
 __global__ void pack_points_kernel(const float* __restrict__ Xs, const float* __restrict__ Cs,
                                    float4* __restrict__ XC, float4* __restrict__ XP, int K, int N,
                                    int NB) {
-  const size_t slots = (size_t)K * NB * 256;
+  const size_t slots = (size_t)K * NB * kRaysThreads;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < slots; k += stride) {
-    const int p = (int)(k & 255);
-    const size_t fb = k >> 8;
+    const int p = (int)(k % kRaysThreads);
+    const size_t fb = k / kRaysThreads;
     const int b = (int)(fb % NB);
     const size_t f = fb / NB;
-    const int nA = b * 512 + p, nB = nA + 256;
+    const int nA = b * kTilePts + p, nB = nA + kRaysThreads;
     float4 A = make_float4(0.f, 0.f, 0.f, 0.f), Bv = A;
     if (nA < N) {
       const float* x = Xs + (f * N + nA) * 3;
@@ -572,7 +596,7 @@ __device__ __forceinline__ void rays_pair(const RaysConst& c, float2 (&S)[28], f
   }
 }
 
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kRaysThreads, kRaysCtasPerSM)
 gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
                                  const float4* __restrict__ XC, const float4* __restrict__ XP,
                                  const int32_t* __restrict__ ii_row,
@@ -617,10 +641,12 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
   if (tid == 0) {
     for (int s = 0; s < kStages; ++s) {
       ptx::mbar_init(&full_bar[s], 1);
-      ptx::mbar_init(&empty_bar[s], kThreads);
+      ptx::mbar_init(&empty_bar[s], kRaysThreads);
     }
     ptx::mbar_fence_init();
+#if FRODO_ABL != 4
     for (int t = 0; t < kStages && t < ntile; ++t) issue_tile(t);
+#endif
   }
 
   const Sim3f Ti = load_pose(Twc, ix);
@@ -674,25 +700,28 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
       long long ia = ip[tid];
       if (st[kOffVm + tid] == 0) ia = 0;  // gn_kernels.cu:677
       ptx::cp_async_16(dst, XCi + ia);
-      if (tid + kThreads < left) {
-        long long ib = ip[tid + kThreads];
-        if (st[kOffVm + tid + kThreads] == 0) ib = 0;
+      if (tid + kRaysThreads < left) {
+        long long ib = ip[tid + kRaysThreads];
+        if (st[kOffVm + tid + kRaysThreads] == 0) ib = 0;
         ptx::cp_async_16(dst + 16u, XCi + ib);
       }
     }
   };
 
+#if FRODO_ABL != 4
 #pragma unroll
   for (int g = 0; g < kGatherDepth; ++g) {
     if (g < ntile) issue_gather(npts - g * kTilePts, g % kStages, g);
     ptx::cp_async_commit();
   }
+#endif
   uint32_t empty_phase = 0;          // producer only
   int s_cur = 0, g_cur = 0;          // stage / gather buffer of tile t
   int s_ahead = kGatherDepth % kStages, g_ahead = kGatherDepth;  // of tile t + kGatherDepth
   int s_prev = kStages - 1;          // stage of tile t - 1
   int left = npts;                   // points from the start of tile t to the end of the span
   for (int t = 0; t < ntile; ++t) {
+#if FRODO_ABL != 4
     if (tid == 0 && t >= 1 && t - 1 + kStages < ntile) {
       // every thread has read its operands of tile t-1: refill that stage
       ptx::mbar_wait(sm_empty + 8u * s_prev, (empty_phase >> s_prev) & 1u);
@@ -702,6 +731,7 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
     if (t + kGatherDepth < ntile) issue_gather(left - kGatherDepth * kTilePts, s_ahead, g_ahead);
     ptx::cp_async_commit();
     ptx::cp_async_wait<kGatherDepth>();  // this thread's gathers of tile t have landed
+#endif
     if (tid < left) {
       const unsigned char* st = stage_raw + s_cur * kStageBytes;
       float4 ja = reinterpret_cast<const float4*>(st + kOffXP)[2 * tid];
@@ -713,10 +743,10 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
       float4 xiB;
       float2 q;
       bool vmA = st[kOffVm + tid] != 0, vmB;
-      if (tid + kThreads < left) {
+      if (tid + kRaysThreads < left) {
         xiB = gb[1];
-        q = f2(qp[tid], qp[tid + kThreads]);
-        vmB = st[kOffVm + tid + kThreads] != 0;
+        q = f2(qp[tid], qp[tid + kRaysThreads]);
+        vmB = st[kOffVm + tid + kRaysThreads] != 0;
       } else {  // ragged tail: lane y repeats lane x with zero weight
         xiB = xiA;
         q = f2(qp[tid], qp[tid]);
@@ -742,8 +772,13 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
   for (int k = 0; k < 28; ++k) S[k] = S2[k].x + S2[k].y;
 #pragma unroll
   for (int k = 0; k < 7; ++k) v[k] = v2[k].x + v2[k].y;
-  edge_epilogue<kThreads>(S, v, Ti, e, chunk, nchunks, nchunks, partials, tickets, edge_blocks);
+  edge_epilogue<kRaysThreads>(S, v, Ti, e, chunk, nchunks, nchunks, partials, tickets, edge_blocks);
 }
+
+
+#if FRODO_RAYS_WS
+#include "gn_accumulate_ws.cuh"
+#endif
 
 }  // namespace
 
@@ -751,15 +786,19 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
 // multiples of the 512-point tile (2 CTAs per SM; the fixed cost ~ 1500 points covers the
 // pipeline fill and the reduction epilogue).
 int gn_pts_per_cta(int E, int N) {
+#if FRODO_RAYS_WS
+  const long long cand[] = {2048, 4096, 8192, 12288, 16384, 24576, 32768, 49152, 65536};
+#else
   const long long cand[] = {2048, 4096, 6144, 8192, 12288, 16384, 24576, 32768};
-  const double slots = 2.0 * kNumSMs;
+#endif
+  const double slots = (double)kRaysCtasPerSM * kNumSMs;
   long long best = 2048;
   double best_cost = 1e300;
   for (long long ppc : cand) {
     const long long nch = ((long long)(N > 0 ? N : 1) + ppc - 1) / ppc;
     const double waves = (double)(nch * (long long)(E > 0 ? E : 1)) / slots;
     const double rounds = waves <= 1.0 ? 1.0 : (double)(long long)(waves + 0.999999);
-    const long long eff = ppc < N ? ppc : ((N + 511) / 512) * 512;
+    const long long eff = ppc < N ? ppc : ((N + kTilePts - 1) / kTilePts) * kTilePts;
     const double cost = rounds * ((double)eff + 1500.0);
     if (cost < best_cost) {
       best_cost = cost;
@@ -780,7 +819,7 @@ int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float*
   const size_t total = (size_t)K * (size_t)N;
   if (total == 0) return FRODO_OK;
   const int NB = (N + kTilePts - 1) / kTilePts;
-  const size_t slots = (size_t)K * NB * 256;
+  const size_t slots = (size_t)K * NB * kRaysThreads;
   const size_t want = (slots + 255) / 256;
   const int blocks = (int)(want < (size_t)(8 * kNumSMs) ? want : (size_t)(8 * kNumSMs));
   float4* xc = reinterpret_cast<float4*>(XC);
@@ -804,16 +843,30 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
         reinterpret_cast<uintptr_t>(Q) | reinterpret_cast<uintptr_t>(valid)) & 15) == 0;
   if (prm.mode == FRODO_GN_RAYS && XC != nullptr && (N % 16) == 0 && aligned16) {
     static bool attr_set = false;
+#if FRODO_RAYS_WS
+    const size_t smem = (size_t)kWsSmemBytes;
+    if (!attr_set) {
+      FRODO_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_rays_ws_kernel,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_set = true;
+    }
+    const int nitems = nchunks * E;
+    gn_accumulate_rays_ws_kernel<<<nitems < kNumSMs ? nitems : kNumSMs, kWsThreads, smem, s>>>(
+        prm, Twc, reinterpret_cast<const float4*>(XC),
+        reinterpret_cast<const float4*>(XC) + (size_t)K * N, ii_row, jj_row, idx, valid, Q, N, ppc,
+        nchunks, nitems, partials, tickets, edge_blocks, done);
+#else
     const size_t smem = (size_t)kRaysSmemBytes;
     if (!attr_set) {
       FRODO_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_rays_packed_kernel,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       attr_set = true;
     }
-    gn_accumulate_rays_packed_kernel<<<grid, kThreads, smem, s>>>(
+    gn_accumulate_rays_packed_kernel<<<grid, kRaysThreads, smem, s>>>(
         prm, Twc, reinterpret_cast<const float4*>(XC),
         reinterpret_cast<const float4*>(XC) + (size_t)K * N, ii_row, jj_row, idx, valid, Q, N, ppc,
         partials, tickets, edge_blocks, done);
+#endif
     FRODO_CUDA_TRY(cudaGetLastError());
     return FRODO_OK;
   }

@@ -103,6 +103,30 @@ __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+// The executing thread arrives on `bar` once all its earlier cp.async copies have landed; the
+// arrival is one of the barrier's expected count (noinc), so the count is the number of
+// threads that do this per phase.
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// Named barrier over `THREADS` threads of the CTA (ids 1..15; 0 is __syncthreads).
+template <int ID, int THREADS>
+__device__ __forceinline__ void named_bar_sync() {
+  asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(THREADS) : "memory");
+}
+
+// Register re-allocation between the warpgroups of a warp-specialised CTA (all four warps of
+// the warpgroup execute it; N a multiple of 8).
+template <int N>
+__device__ __forceinline__ void setmaxnreg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
+}
+template <int N>
+__device__ __forceinline__ void setmaxnreg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
+}
+
 // Orders generic-proxy accesses (plain ld/st) against async-proxy accesses (bulk copies).
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async;" ::: "memory");
