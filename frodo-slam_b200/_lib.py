@@ -21,6 +21,13 @@ class GnParams(ctypes.Structure):
 
 GN_RAYS, GN_POINTS, GN_CALIB = 0, 1, 2
 
+
+class MatchParams(ctypes.Structure):
+    """struct frodo_match_params (include/frodo_b200.h)."""
+    _fields_ = [("max_iter", c_int), ("lambda_init", c_float), ("convergence_thresh", c_float),
+                ("dist_thresh", c_float), ("radius", c_int), ("dilation_max", c_int),
+                ("ft_matching_threshold", c_float)]
+
 # name -> (restype, argtypes); kept in sync with include/frodo_b200.h (tests check this)
 SIGNATURES = {
     "frodo_version": (c_int, []),
@@ -28,6 +35,15 @@ SIGNATURES = {
     "frodo_iter_proj": (c_int, [c_void_p] * 5 + [c_int] * 5 + [c_float, c_float, c_void_p]),
     "frodo_refine_matches_f16": (c_int, [c_void_p] * 5 + [c_int] * 7 + [c_void_p]),
     "frodo_refine_matches_f32": (c_int, [c_void_p] * 5 + [c_int] * 7 + [c_void_p]),
+    "frodo_match_prep": (c_int, [c_void_p] * 6 + [c_int] * 3 + [c_void_p]),
+    "frodo_match_occlusion": (c_int, [c_void_p] * 4 + [c_float, c_void_p, c_void_p] + [c_int] * 3 +
+                              [c_void_p]),
+    "frodo_convert_f32_f16": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
+    "frodo_match_finish": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_float, c_void_p,
+                                   c_void_p] + [c_int] * 3 + [c_void_p]),
+    "frodo_match_workspace_bytes": (c_size_t, [c_int] * 4),
+    "frodo_match": (c_int, [ctypes.POINTER(MatchParams)] + [c_void_p] * 7 + [c_int] * 4 +
+                    [c_void_p, c_size_t, c_void_p]),
     "frodo_gn_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "frodo_gn_workspace_init": (c_int, [c_void_p, c_size_t, c_int, c_int, c_int, c_void_p]),
     "frodo_gn_edge_index": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,

@@ -99,6 +99,118 @@ int frodo_refine_matches_f32(const float* D11, const float* D21, const int64_t* 
                            static_cast<cudaStream_t>(stream));
 }
 
+// ---- the matching pipeline around the kernels (matching.py:25-110) ----------------------
+int frodo_match_prep(const float* X11, const float* X21, const int64_t* idx_1_to_2_init,
+                     float* rays_with_grad, float* pts3d_norm, float* p_init, int B, int H, int W,
+                     frodo_stream_t stream) {
+  FRODO_ARG_CHECK(B >= 0 && B <= 65535 && H >= 2 && W >= 2);
+  FRODO_ARG_CHECK(B == 0 || (X11 && X21 && rays_with_grad && pts3d_norm && p_init));
+  return launch_match_prep(X11, X21, idx_1_to_2_init, rays_with_grad, pts3d_norm, p_init, B, H, W,
+                           static_cast<cudaStream_t>(stream));
+}
+
+int frodo_match_occlusion(const float* X11, const float* X21, const float* p_iter,
+                          const uint8_t* converged, float dist_thresh, int64_t* p1, uint8_t* valid,
+                          int B, int H, int W, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(B >= 0 && H >= 1 && W >= 1);
+  FRODO_ARG_CHECK(B == 0 || (X11 && X21 && p_iter && converged && p1 && valid));
+  return launch_match_occlusion(X11, X21, p_iter, converged, dist_thresh, p1, valid, B, H, W,
+                                static_cast<cudaStream_t>(stream));
+}
+
+int frodo_convert_f32_f16(const float* src, void* dst, size_t n, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(n == 0 || (src && dst));
+  return launch_convert_f32_f16(src, static_cast<__half*>(dst), n,
+                                static_cast<cudaStream_t>(stream));
+}
+
+int frodo_match_finish(const int64_t* p1, const void* scores, int scores_f16,
+                       const uint8_t* valid_in, float threshold, int64_t* idx_1_to_2,
+                       uint8_t* valid, int B, int N, int W, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(B >= 0 && N >= 0 && W >= 1);
+  FRODO_ARG_CHECK(B == 0 || N == 0 || (p1 && scores && valid_in && idx_1_to_2 && valid));
+  return launch_match_finish(p1, scores, scores_f16 != 0, valid_in, threshold, idx_1_to_2, valid,
+                             B, N, W, static_cast<cudaStream_t>(stream));
+}
+
+namespace {
+// Workspace of frodo_match, carved in this order (each piece 256-byte aligned).
+struct MatchCarve {
+  size_t rays, pts, p_init, p_iter, conv, p1, valid, d11h, d21h, p1_new, scores, total;
+};
+MatchCarve match_carve(int B, int H, int W, int F) {
+  const size_t px = (size_t)(B > 0 ? B : 0) * (size_t)H * (size_t)W;
+  MatchCarve c;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    const size_t at = off;
+    off += (bytes + 255) & ~(size_t)255;
+    return at;
+  };
+  c.rays = take(px * 36);
+  c.pts = take(px * 12);
+  c.p_init = take(px * 8);
+  c.p_iter = take(px * 8);
+  c.conv = take(px);
+  c.p1 = take(px * 16);
+  c.valid = take(px);
+  c.d11h = take(px * (size_t)F * 2);
+  c.d21h = take(px * (size_t)F * 2);
+  c.p1_new = take(px * 16);
+  c.scores = take(px * 2);
+  c.total = off;
+  return c;
+}
+}  // namespace
+
+size_t frodo_match_workspace_bytes(int B, int H, int W, int F) {
+  if (B < 0 || H < 1 || W < 1 || F < 1) return 0;
+  return match_carve(B, H, W, F).total;
+}
+
+int frodo_match(const frodo_match_params* prm, const float* X11, const float* X21,
+                const float* D11, const float* D21, const int64_t* idx_1_to_2_init,
+                int64_t* idx_1_to_2, uint8_t* valid, int B, int H, int W, int F, void* workspace,
+                size_t workspace_bytes, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(prm != nullptr);
+  FRODO_ARG_CHECK(B >= 0 && B <= 65535 && H >= 3 && W >= 3 && F >= 1);
+  FRODO_ARG_CHECK(prm->radius >= 1 && prm->dilation_max >= 1 && prm->max_iter >= 0);
+  if (B == 0) return FRODO_OK;
+  FRODO_ARG_CHECK(X11 && X21 && D11 && D21 && idx_1_to_2 && valid && workspace);
+  const MatchCarve c = match_carve(B, H, W, F);
+  FRODO_ARG_CHECK(workspace_bytes >= c.total);
+  FRODO_ARG_CHECK((reinterpret_cast<uintptr_t>(workspace) & 255) == 0);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  float* rays = reinterpret_cast<float*>(ws + c.rays);
+  float* pts = reinterpret_cast<float*>(ws + c.pts);
+  float* p_init = reinterpret_cast<float*>(ws + c.p_init);
+  float* p_iter = reinterpret_cast<float*>(ws + c.p_iter);
+  uint8_t* conv = ws + c.conv;
+  int64_t* p1 = reinterpret_cast<int64_t*>(ws + c.p1);
+  uint8_t* v0 = ws + c.valid;
+  __half* d11h = reinterpret_cast<__half*>(ws + c.d11h);
+  __half* d21h = reinterpret_cast<__half*>(ws + c.d21h);
+  int64_t* p1_new = reinterpret_cast<int64_t*>(ws + c.p1_new);
+  __half* scores = reinterpret_cast<__half*>(ws + c.scores);
+  const int N = H * W;
+  const size_t nd = (size_t)B * N * F;
+  int rc;
+  if ((rc = launch_match_prep(X11, X21, idx_1_to_2_init, rays, pts, p_init, B, H, W, s))) return rc;
+  if ((rc = launch_iter_proj(rays, pts, p_init, p_iter, conv, B, H, W, N, prm->max_iter,
+                             prm->lambda_init, prm->convergence_thresh, s)))
+    return rc;
+  if ((rc = launch_match_occlusion(X11, X21, p_iter, conv, prm->dist_thresh, p1, v0, B, H, W, s)))
+    return rc;
+  if ((rc = launch_convert_f32_f16(D11, d11h, nd, s))) return rc;
+  if ((rc = launch_convert_f32_f16(D21, d21h, nd, s))) return rc;
+  if ((rc = launch_refine_f16(d11h, d21h, p1, p1_new, scores, B, H, W, N, F, prm->radius,
+                              prm->dilation_max, s)))
+    return rc;
+  return launch_match_finish(p1_new, scores, true, v0, prm->ft_matching_threshold, idx_1_to_2,
+                             valid, B, N, W, s);
+}
+
 size_t frodo_gn_workspace_bytes(int K, int E, int N) {
   return gn_carve_workspace(nullptr, K, E, N, nullptr);
 }

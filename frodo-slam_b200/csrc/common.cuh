@@ -43,4 +43,15 @@ int launch_refine_f32(const float* D11, const float* D21, const int64_t* p1, int
                       float* scores, int B, int H, int W, int N, int F, int radius, int dil,
                       cudaStream_t s);
 
+int launch_match_prep(const float* X11, const float* X21, const int64_t* idx_init,
+                      float* rays_with_grad, float* pts3d_norm, float* p_init, int B, int H, int W,
+                      cudaStream_t s);
+int launch_match_occlusion(const float* X11, const float* X21, const float* p_iter,
+                           const uint8_t* conv, float dist_thresh, int64_t* p1, uint8_t* valid,
+                           int B, int H, int W, cudaStream_t s);
+int launch_convert_f32_f16(const float* src, __half* dst, size_t n, cudaStream_t s);
+int launch_match_finish(const int64_t* p1, const void* scores, bool scores_f16,
+                        const uint8_t* valid_in, float threshold, int64_t* idx, uint8_t* valid,
+                        int B, int N, int W, cudaStream_t s);
+
 }  // namespace frodo

@@ -63,6 +63,54 @@ int frodo_refine_matches_f32(const float* D11, const float* D21, const int64_t* 
                              int64_t* p1_new, float* max_scores, int B, int H, int W, int N, int F,
                              int radius, int dilation_max, frodo_stream_t stream);
 
+/* ---- the matching pipeline around the two kernels ----------
+ * mast3r_slam/matching.py:25-110 + mast3r_slam/image.py:5-38, which the reference runs as
+ * ~20 PyTorch kernels per call.  The arithmetic order is fixed, every product and sum
+ * rounded separately (no FMA): |x|^2 = (x0 x0 + x1 x1) + x2 x2, IEEE sqrt and division,
+ * x / max(|x|, 1e-12); Scharr taps (3/32, 10/32) accumulated in row-major order, zero taps
+ * skipped.  torch orders the same sums differently, so against the reference the float
+ * outputs agree to 1-2 ulp and the final indices / masks are identical on the golden
+ * vectors (tests/golden/golden_match.npz); against the CPU restatement under oracle/ (same
+ * order) every output is bit-identical.
+ *
+ * frodo_match_prep: prep_for_iter_proj (matching.py:25-49).  X11, X21 [B,H,W,3] f32;
+ *   idx_1_to_2_init [B,H*W] i64 or NULL (identity).  Outputs rays_with_grad [B,H,W,9]
+ *   (normalised ray, Scharr d/dx, d/dy with reflect padding), pts3d_norm [B,H*W,3],
+ *   p_init [B,H*W,2] f32 (x, y).  H, W >= 2.
+ * frodo_match_occlusion: matching.py:66-75.  p1 [B,H*W,2] i64 = trunc(p_iter);
+ *   valid = converged & (||X11[p1] - X21|| < dist_thresh).
+ * frodo_convert_f32_f16: tensor.half() (matching.py:79-80), round to nearest even.
+ * frodo_match_finish: matching.py:87-92.  valid = valid_in & (score > threshold, compared
+ *   in the scores' dtype), idx_1_to_2 = x + W * y.  scores_f16 != 0: scores are fp16.
+ * frodo_match: match() (matching.py:8-10) = all of the above + iter_proj + refine_matches
+ *   (fp16 descriptors) in one call; D11 [B,H,W,F], D21 [B,H,W,F] f32; outputs idx_1_to_2
+ *   [B,H*W] i64 and valid [B,H*W] u8; workspace of frodo_match_workspace_bytes(B,H,W,F). */
+typedef struct frodo_match_params {
+  int max_iter;
+  float lambda_init;
+  float convergence_thresh;
+  float dist_thresh;
+  int radius;       /* 0: no refinement is not supported by match() in the reference either */
+  int dilation_max;
+  float ft_matching_threshold;
+} frodo_match_params;
+
+int frodo_match_prep(const float* X11, const float* X21, const int64_t* idx_1_to_2_init,
+                     float* rays_with_grad, float* pts3d_norm, float* p_init, int B, int H, int W,
+                     frodo_stream_t stream);
+int frodo_match_occlusion(const float* X11, const float* X21, const float* p_iter,
+                          const uint8_t* converged, float dist_thresh, int64_t* p1, uint8_t* valid,
+                          int B, int H, int W, frodo_stream_t stream);
+int frodo_convert_f32_f16(const float* src, void* dst, size_t n, frodo_stream_t stream);
+int frodo_match_finish(const int64_t* p1, const void* scores, int scores_f16,
+                       const uint8_t* valid_in, float threshold, int64_t* idx_1_to_2,
+                       uint8_t* valid, int B, int N, int W, frodo_stream_t stream);
+size_t frodo_match_workspace_bytes(int B, int H, int W, int F);
+int frodo_match(const frodo_match_params* params, const float* X11, const float* X21,
+                const float* D11, const float* D21, const int64_t* idx_1_to_2_init,
+                int64_t* idx_1_to_2, uint8_t* valid, int B, int H, int W, int F, void* workspace,
+                size_t workspace_bytes, frodo_stream_t stream);
+
 /* ---- Gauss-Newton over the keyframe graph ---------------------------------
  * Shared tensor meanings (gn_kernels.cu:909-995):
  *   Twc [K,8] f32 = [t(3), q_xyzw(4), s], updated IN PLACE;  Xs [K,N,3] f32;

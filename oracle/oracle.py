@@ -281,3 +281,97 @@ def gauss_newton_rays_odom(Twc, Xs, Cs, ii, jj, idx, valid, Q, odom_ii, odom_jj,
         if np.float32(np.sqrt(np.sum(dx.astype(np.float64) ** 2))) < delta_thresh:
             break
     return dict(Twc=Twc, dx=dx, iters=iters, fails=fails)
+
+
+# ---------------------------------------------------------------------------
+# The matching pipeline around the two kernels: restatement of
+# mast3r_slam/matching.py:25-110 and mast3r_slam/image.py:5-38 in numpy fp32 with a FIXED
+# operation order (every product and sum rounded separately, no FMA), which the CUDA kernels of
+# csrc/match_glue.cu follow bit for bit.  torch's own kernels use other orders, so against the
+# reference's outputs (tests/golden/golden_match.npz) the prologue agrees to 1-2 ulp, not bitwise.
+# ---------------------------------------------------------------------------
+_F = np.float32
+
+
+def normalize3(x):
+    """F.normalize(x, dim=-1) (matching.py:30,42): x / max(||x||_2, 1e-12)."""
+    x = np.asarray(x, _F)
+    n2 = ((x[..., 0] * x[..., 0] + x[..., 1] * x[..., 1]).astype(_F)
+          + x[..., 2] * x[..., 2]).astype(_F)
+    d = np.maximum(np.sqrt(n2).astype(_F), _F(1e-12))
+    return (x / d[..., None]).astype(_F)
+
+
+def img_gradient(img):
+    """image.py:5-38 on a channels-last image [b,h,w,c]: Scharr kernels / 32, reflect padding.
+    Taps are accumulated in row-major order, zero taps skipped."""
+    img = np.asarray(img, _F)
+    h, w = img.shape[1], img.shape[2]
+    pad = np.pad(img, ((0, 0), (1, 1), (1, 1), (0, 0)), mode="reflect")
+    w3, w10 = _F(3.0 / 32.0), _F(10.0 / 32.0)
+
+    def tap(dy, dx):
+        return pad[:, dy:dy + h, dx:dx + w, :]
+
+    gx = np.zeros_like(img)
+    for dy, dx, wt in ((0, 0, -w3), (0, 2, w3), (1, 0, -w10), (1, 2, w10), (2, 0, -w3), (2, 2, w3)):
+        gx = (gx + (tap(dy, dx) * wt).astype(_F)).astype(_F)
+    gy = np.zeros_like(img)
+    for dy, dx, wt in ((0, 0, -w3), (0, 1, -w10), (0, 2, -w3), (2, 0, w3), (2, 1, w10), (2, 2, w3)):
+        gy = (gy + (tap(dy, dx) * wt).astype(_F)).astype(_F)
+    return gx, gy
+
+
+def prep_for_iter_proj(X11, X21, idx_1_to_2_init=None):
+    """matching.py:25-49.  Returns rays_with_grad_img [b,h,w,9], pts3d_norm [b,hw,3],
+    p_init [b,hw,2] (x, y) float32."""
+    X11 = np.asarray(X11, _F)
+    b, h, w, _ = X11.shape
+    rays = normalize3(X11)
+    gx, gy = img_gradient(rays)
+    rays_with_grad = np.ascontiguousarray(np.concatenate([rays, gx, gy], axis=-1))
+    pts = normalize3(np.asarray(X21, _F).reshape(b, h * w, 3))
+    if idx_1_to_2_init is None:
+        idx_1_to_2_init = np.tile(np.arange(h * w, dtype=np.int64)[None], (b, 1))
+    idx0 = np.asarray(idx_1_to_2_init, np.int64)
+    p_init = np.stack([idx0 % w, idx0 // w], axis=-1).astype(_F)
+    return rays_with_grad, pts, p_init
+
+
+def match_occlusion(X11, X21, p_iter, conv, dist_thresh):
+    """matching.py:66-75: p1 = trunc(p), valid = converged & ||X11[p1] - X21|| < dist_thresh."""
+    X11 = np.asarray(X11, _F)
+    b, h, w, _ = X11.shape
+    p1 = np.trunc(np.asarray(p_iter, _F)).astype(np.int64)
+    bi = np.arange(b)[:, None]
+    d = (X11[bi, p1[..., 1], p1[..., 0], :] - np.asarray(X21, _F).reshape(b, h * w, 3)).astype(_F)
+    n2 = ((d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1]).astype(_F)
+          + d[..., 2] * d[..., 2]).astype(_F)
+    dist = np.sqrt(n2).astype(_F)
+    return p1, np.asarray(conv, bool) & (dist < _F(dist_thresh))
+
+
+def match_finish(p1, scores, valid, w, ft_matching_threshold):
+    """matching.py:87-92: valid &= score > threshold (compared in the scores' dtype),
+    idx = x + w * y.  Returns (idx [b,hw] int64, valid [b,hw,1] bool)."""
+    scores = np.asarray(scores)
+    thr = scores.dtype.type(ft_matching_threshold)
+    v = np.asarray(valid, bool) & (scores > thr)
+    p1 = np.asarray(p1, np.int64)
+    return p1[..., 0] + w * p1[..., 1], v[..., None]
+
+
+def match(X11, X21, D11, D21, idx_1_to_2_init=None, max_iter=10, lambda_init=1e-8,
+          convergence_thresh=1e-6, dist_thresh=0.1, radius=3, dilation_max=5,
+          ft_matching_threshold=0.8):
+    """matching.py:8-10, 52-95 (match -> match_iterative_proj).  D11/D21 any float dtype; they
+    are rounded to fp16 as the reference does (matching.py:79-80)."""
+    X11 = np.asarray(X11, _F)
+    b, h, w, _ = X11.shape
+    rays, pts, p_init = prep_for_iter_proj(X11, X21, idx_1_to_2_init)
+    p, conv = iter_proj(rays, pts, p_init, max_iter, lambda_init, convergence_thresh)
+    p1, valid = match_occlusion(X11, X21, p, conv, dist_thresh)
+    D11h = np.asarray(D11).astype(np.float16)
+    D21h = np.asarray(D21).astype(np.float16).reshape(b, h * w, -1)
+    p1, scores = refine_matches(D11h, D21h, p1, radius, dilation_max)
+    return match_finish(p1, scores, valid, w, ft_matching_threshold)

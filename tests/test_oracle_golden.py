@@ -6,6 +6,7 @@ import numpy as np
 import pytest
 
 from helpers import GP, MP, rel_err
+from oracle import oracle
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden", "golden_ref.npz")
 
@@ -91,3 +92,38 @@ def test_gn_rays_odom_oracle_matches_reference(num_fix, iters):
     if iters == 1:
         assert rel_err(r["dx"], gd[f"odom_fix{num_fix}_it{iters}_dx"]) < 1e-4
     assert np.array_equal(r["Twc"][:num_fix], gd["gn_Twc"][:num_fix])
+
+
+# ------------------------------------------------ match() pipeline (golden_match.npz)
+GOLD_MATCH = os.path.join(os.path.dirname(__file__), "golden", "golden_match.npz")
+
+
+def _match_cfg(g):
+    c = {k[4:]: float(g[k]) for k in g.files if k.startswith("cfg_")}
+    for k in ("max_iter", "radius", "dilation_max"):
+        c[k] = int(c[k])
+    return c
+
+
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_match_pipeline_oracle_vs_reference_python(tag):
+    """Recorded from the reference's own matching.py / image.py (CPU torch) by
+    tests/golden/make_golden_match.py.  Prologue: torch orders the sums differently, 2 ulp;
+    the tail on the recorded intermediates and the whole pipeline: identical indices and masks."""
+    g = np.load(GOLD_MATCH)
+    c = _match_cfg(g)
+    init = None if tag == "a" else g["idx_init"]
+    rays, pts, p_init = oracle.prep_for_iter_proj(g["X11"], g["X21"], init)
+    assert np.abs(rays - g[tag + "_rays_with_grad_img"]).max() <= 2.4e-7   # values are <= 1
+    assert np.abs(pts - g[tag + "_pts3d_norm"]).max() <= 2.4e-7
+    assert np.array_equal(p_init, g[tag + "_p_init"])
+    p1, v = oracle.match_occlusion(g["X11"], g["X21"], g[tag + "_p_iter"], g[tag + "_conv"],
+                                   c["dist_thresh"])
+    idx, valid = oracle.match_finish(g[tag + "_p_refined"], g[tag + "_scores"], v,
+                                     g["X11"].shape[2], c["ft_matching_threshold"])
+    assert np.array_equal(idx, g[tag + "_idx_1_to_2"])
+    assert np.array_equal(valid, g[tag + "_valid"])
+    idx2, valid2 = oracle.match(g["X11"], g["X21"], g["D11"], g["D21"], init, **c)
+    assert np.array_equal(idx2, g[tag + "_idx_1_to_2"])
+    assert np.array_equal(valid2, g[tag + "_valid"])
+    assert 0.2 < valid2.mean() < 0.95   # the fixture exercises both outcomes
