@@ -313,7 +313,7 @@ def main_ours(args):
     ms_acc = timed_steps(acc_only, n_acc, 3) / n_acc
     bytes_launch = GN_BYTES_PER_POINT * N_PTS * sg.E_local
     achieved = bytes_launch / (ms_acc * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "gn_accumulate_rays_packed_kernel", "achieved": achieved,
+    roofline = {"bound": "hbm", "kernel": "gn_accumulate_packed_kernel<rays>", "achieved": achieved,
                 "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None, "us_per_launch": ms_acc * 1e3,
                 "algorithmic_bytes_per_launch": bytes_launch,

@@ -245,7 +245,7 @@ def gn_system(params, Twc, Xs, Cs, K, ii, jj, idx_ii2jj, valid_match, Q, num_fix
         _lib.check(lib.frodo_gn_edge_index(_ptr(ii), _ptr(jj), E, _ptr(ii_row), _ptr(jj_row), None,
                                            st))
         xc = None
-        if params.mode == GN_RAYS and N % 16 == 0 and E > 0:
+        if N % 16 == 0 and E > 0:
             off = lib.frodo_gn_workspace_packed_offset(num_kf, E, N)
             xc = ctypes.c_void_p(ws.data_ptr() + off)
             _lib.check(lib.frodo_gn_pack_points(_ptr(Xs), _ptr(Cs), num_kf, N, xc, st))

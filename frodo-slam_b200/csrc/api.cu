@@ -320,9 +320,9 @@ static int gn_run(const frodo_gn_params* params, float* Twc, const float* Xs, co
     rc = launch_gn_edge_index(ii, jj, E, ws.ii_row, ws.jj_row, ws.scalars, s);
   }
   if (rc) return rc;
-  // rays fast path: repack the pointmaps once per solve (they do not change across iterations)
+  // packed fast path: repack the pointmaps once per solve (they do not change across iterations)
   const float* XC = nullptr;
-  if (params->mode == FRODO_GN_RAYS && E > 0 && N > 0 && (N % 16) == 0 && max_iter > 0) {
+  if (E > 0 && N > 0 && (N % 16) == 0 && max_iter > 0) {
     rc = launch_gn_pack_points(Xs, Cs, K, N, ws.packed, s);
     if (rc) return rc;
     XC = ws.packed;

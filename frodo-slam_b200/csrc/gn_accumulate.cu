@@ -205,10 +205,12 @@ __device__ __forceinline__ float rsqrt_fast(float x) {
   return y;
 }
 
-struct RaysConst {
+struct RaysConst {  // per-edge constants of the packed kernels (all three modes)
   float M[9];  // s_ij R(q_ij)
   float t[3];
   float sa2, sb2, C_thresh, Q_thresh;
+  float fx, fy, cx, cy, ulo, uhi, vlo, vhi, z_eps;  // calib only
+  unsigned width, width_rcp;                         // calib only; floor(2^32 / width)
 };
 
 __host__ __device__ constexpr int tri(int n, int m) { return n * 7 - n * (n - 1) / 2 + (m - n); }
@@ -596,8 +598,95 @@ __device__ __forceinline__ void rays_pair(const RaysConst& c, float2 (&S)[28], f
   }
 }
 
+// Points mode (gn_kernels.cu:2031-2158), two points per thread: e = P - Xi, three rows
+// [e_a | -[P]x row a | P_a].
+__device__ __forceinline__ void points_pair(const RaysConst& c, float2 (&S)[28], float2 (&v)[7],
+                                            const float4 xiA, const float4 xiB, float2 xj0,
+                                            float2 xj1, float2 xj2, float2 cj, float2 q, bool vmA,
+                                            bool vmB) {
+  const float2 P0 = fma2(bc(c.M[0]), xj0, fma2(bc(c.M[1]), xj1, fma2(bc(c.M[2]), xj2, bc(c.t[0]))));
+  const float2 P1 = fma2(bc(c.M[3]), xj0, fma2(bc(c.M[4]), xj1, fma2(bc(c.M[5]), xj2, bc(c.t[1]))));
+  const float2 P2 = fma2(bc(c.M[6]), xj0, fma2(bc(c.M[7]), xj1, fma2(bc(c.M[8]), xj2, bc(c.t[2]))));
+  const float2 e0 = f2(P0.x - xiA.x, P0.y - xiB.x);
+  const float2 e1 = f2(P1.x - xiA.y, P1.y - xiB.y);
+  const float2 e2 = f2(P2.x - xiA.z, P2.y - xiB.z);
+  const bool okA = vmA & (q.x > c.Q_thresh) & (xiA.w > c.C_thresh) & (cj.x > c.C_thresh);
+  const bool okB = vmB & (q.y > c.Q_thresh) & (xiB.w > c.C_thresh) & (cj.y > c.C_thresh);
+  const float2 ws = mul2(bc(c.sa2), f2(okA ? q.x : 0.0f, okB ? q.y : 0.0f));
+  const float2 w0 = huber_w2(ws, e0), w1 = huber_w2(ws, e1), w2 = huber_w2(ws, e2);
+  const float2 z = f2(0.f, 0.f), one = f2(1.f, 1.f);
+  const float2 n0 = mul2(P0, bc(-1.0f)), n1 = mul2(P1, bc(-1.0f)), n2 = mul2(P2, bc(-1.0f));
+  {
+    const float2 x[7] = {one, z, z, z, P2, n1, P0};
+    pair_row<0x71u>(S, v, x, w0, e0);  // {0,4,5,6}
+  }
+  {
+    const float2 x[7] = {z, one, z, n2, z, P0, P1};
+    pair_row<0x6Au>(S, v, x, w1, e1);  // {1,3,5,6}
+  }
+  {
+    const float2 x[7] = {z, z, one, P1, n0, z, P2};
+    pair_row<0x5Cu>(S, v, x, w2, e2);  // {2,3,4,6}
+  }
+}
+
+// Calibrated mode (gn_kernels.cu:2410-2561), two points per thread: pixel residual of the
+// projection of P against the target pixel (ind % width, ind / width), log-depth residual.
+__device__ __forceinline__ void calib_pair(const RaysConst& c, float2 (&S)[28], float2 (&v)[7],
+                                           const float4 xiA, const float4 xiB, float2 xj0,
+                                           float2 xj1, float2 xj2, float2 cj, float2 q, bool vmA,
+                                           bool vmB, unsigned indA, unsigned indB) {
+  const float2 P0 = fma2(bc(c.M[0]), xj0, fma2(bc(c.M[1]), xj1, fma2(bc(c.M[2]), xj2, bc(c.t[0]))));
+  const float2 P1 = fma2(bc(c.M[3]), xj0, fma2(bc(c.M[4]), xj1, fma2(bc(c.M[5]), xj2, bc(c.t[1]))));
+  const float2 P2 = fma2(bc(c.M[6]), xj0, fma2(bc(c.M[7]), xj1, fma2(bc(c.M[8]), xj2, bc(c.t[2]))));
+  const bool zA = (P2.x > c.z_eps) && (xiA.z > c.z_eps);
+  const bool zB = (P2.y > c.z_eps) && (xiB.z > c.z_eps);
+  // 1/z and log(z_j / z_i) through the special-function unit (1-2 ulp; the bar is 1e-4)
+  const float2 zinv = f2(zA ? __fdividef(1.0f, P2.x) : 0.0f, zB ? __fdividef(1.0f, P2.y) : 0.0f);
+  const float2 e2 = f2(zA ? __logf(__fdividef(P2.x, xiA.z)) : 0.0f,
+                       zB ? __logf(__fdividef(P2.y, xiB.z)) : 0.0f);
+  const float2 xz = mul2(P0, zinv), yz = mul2(P1, zinv);
+  const float2 u = fma2(bc(c.fx), xz, bc(c.cx)), vv = fma2(bc(c.fy), yz, bc(c.cy));
+  // ind = v_t * width + u_t: quotient estimate from floor(2^32 / width), one correction
+  unsigned vtA = __umulhi(indA, c.width_rcp), vtB = __umulhi(indB, c.width_rcp);
+  unsigned utA = indA - vtA * c.width, utB = indB - vtB * c.width;
+  if (utA >= c.width) { utA -= c.width; ++vtA; }
+  if (utB >= c.width) { utB -= c.width; ++vtB; }
+  const float2 e0 = f2(u.x - (float)utA, u.y - (float)utB);
+  const float2 e1 = f2(vv.x - (float)vtA, vv.y - (float)vtB);
+  const bool inA = (u.x > c.ulo) && (u.x < c.uhi) && (vv.x > c.vlo) && (vv.x < c.vhi) && zA;
+  const bool inB = (u.y > c.ulo) && (u.y < c.uhi) && (vv.y > c.vlo) && (vv.y < c.vhi) && zB;
+  const bool okA = inA & vmA & (q.x > c.Q_thresh) & (xiA.w > c.C_thresh) & (cj.x > c.C_thresh);
+  const bool okB = inB & vmB & (q.y > c.Q_thresh) & (xiB.w > c.C_thresh) & (cj.y > c.C_thresh);
+  const float2 wq = f2(okA ? q.x : 0.0f, okB ? q.y : 0.0f);
+  const float2 wp = mul2(bc(c.sa2), wq), wd = mul2(bc(c.sb2), wq);
+  const float2 w0 = huber_w2(wp, e0), w1 = huber_w2(wp, e1), w2 = huber_w2(wd, e2);
+  const float2 z = f2(0.f, 0.f), one = f2(1.f, 1.f);
+  const float2 fxz = mul2(bc(c.fx), zinv), fyz = mul2(bc(c.fy), zinv);
+  const float2 fxxz = mul2(bc(c.fx), xz), fyyz = mul2(bc(c.fy), yz);
+  {
+    // [fx/z, 0, -fx x/z^2, -fx xz yz, fx (1 + xz^2), -fx yz, 0]
+    const float2 x[7] = {fxz, z, mul2(mul2(fxxz, zinv), bc(-1.0f)), mul2(mul2(fxxz, yz), bc(-1.0f)),
+                         fma2(fxxz, xz, bc(c.fx)), mul2(mul2(bc(c.fx), yz), bc(-1.0f)), z};
+    pair_row<0x3Du>(S, v, x, w0, e0);  // {0,2,3,4,5}
+  }
+  {
+    // [0, fy/z, -fy y/z^2, -fy (1 + yz^2), fy xz yz, fy xz, 0]
+    const float2 x[7] = {z, fyz, mul2(mul2(fyyz, zinv), bc(-1.0f)),
+                         mul2(fma2(fyyz, yz, bc(c.fy)), bc(-1.0f)), mul2(fyyz, xz),
+                         mul2(bc(c.fy), xz), z};
+    pair_row<0x3Eu>(S, v, x, w1, e1);  // {1,2,3,4,5}
+  }
+  {
+    const float2 x[7] = {z, z, zinv, yz, mul2(xz, bc(-1.0f)), z, one};
+    pair_row<0x5Cu>(S, v, x, w2, e2);  // {2,3,4,6}
+  }
+}
+
+template <int MODE>
 __global__ void __launch_bounds__(kRaysThreads, kRaysCtasPerSM)
-gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
+gn_accumulate_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
+                            const float* __restrict__ Kmat,
                                  const float4* __restrict__ XC, const float4* __restrict__ XP,
                                  const int32_t* __restrict__ ii_row,
                                  const int32_t* __restrict__ jj_row,
@@ -666,11 +755,20 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
     c.M[7] = s * (2.f * (qy * qz + qx * qw));
     c.M[8] = s * (1.f - 2.f * (qx * qx + qy * qy));
     c.t[0] = Tij.t[0]; c.t[1] = Tij.t[1]; c.t[2] = Tij.t[2];
-    const float sa = 1.0f / prm.sigma_a, sb = 1.0f / prm.sigma_b;
+    const float sa = 1.0f / prm.sigma_a;
+    const float sb = (MODE == FRODO_GN_POINTS) ? 0.0f : 1.0f / prm.sigma_b;
     c.sa2 = sa * sa;
     c.sb2 = sb * sb;
     c.C_thresh = prm.C_thresh;
     c.Q_thresh = prm.Q_thresh;
+    if (MODE == FRODO_GN_CALIB) {
+      c.fx = __ldg(Kmat + 0); c.fy = __ldg(Kmat + 4); c.cx = __ldg(Kmat + 2); c.cy = __ldg(Kmat + 5);
+      c.ulo = (float)prm.pixel_border; c.uhi = (float)(prm.width - 1 - prm.pixel_border);
+      c.vlo = (float)prm.pixel_border; c.vhi = (float)(prm.height - 1 - prm.pixel_border);
+      c.z_eps = prm.z_eps;
+      c.width = prm.width > 1 ? (unsigned)prm.width : 1u;
+      c.width_rcp = c.width > 1 ? (unsigned)(0x100000000ull / c.width) : 0xffffffffu;
+    }
   }
   float2 S2[28], v2[7];
 #pragma unroll
@@ -743,10 +841,15 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
       float4 xiB;
       float2 q;
       bool vmA = st[kOffVm + tid] != 0, vmB;
+      unsigned indA = 0, indB = 0;  // target pixel of the match (calib), low word of idx
+      if (MODE == FRODO_GN_CALIB)
+        indA = reinterpret_cast<const unsigned*>(st + kOffIdx)[2 * tid];
       if (tid + kRaysThreads < left) {
         xiB = gb[1];
         q = f2(qp[tid], qp[tid + kRaysThreads]);
         vmB = st[kOffVm + tid + kRaysThreads] != 0;
+        if (MODE == FRODO_GN_CALIB)
+          indB = reinterpret_cast<const unsigned*>(st + kOffIdx)[2 * (tid + kRaysThreads)];
       } else {  // ragged tail: lane y repeats lane x with zero weight
         xiB = xiA;
         q = f2(qp[tid], qp[tid]);
@@ -755,8 +858,15 @@ gn_accumulate_rays_packed_kernel(frodo_gn_params prm, const float* __restrict__ 
         jb = make_float4(jb.x, jb.x, jb.z, jb.z);
       }
       ptx::mbar_arrive(sm_empty + 8u * s_cur);  // operands are in registers
-      rays_pair(c, S2, v2, xiA, xiB, f2(ja.x, ja.y), f2(ja.z, ja.w), f2(jb.x, jb.y),
-                f2(jb.z, jb.w), q, vmA, vmB);
+      if (MODE == FRODO_GN_RAYS)
+        rays_pair(c, S2, v2, xiA, xiB, f2(ja.x, ja.y), f2(ja.z, ja.w), f2(jb.x, jb.y),
+                  f2(jb.z, jb.w), q, vmA, vmB);
+      else if (MODE == FRODO_GN_POINTS)
+        points_pair(c, S2, v2, xiA, xiB, f2(ja.x, ja.y), f2(ja.z, ja.w), f2(jb.x, jb.y),
+                    f2(jb.z, jb.w), q, vmA, vmB);
+      else
+        calib_pair(c, S2, v2, xiA, xiB, f2(ja.x, ja.y), f2(ja.z, ja.w), f2(jb.x, jb.y),
+                   f2(jb.z, jb.w), q, vmA, vmB, vmA ? indA : 0u, vmB ? indB : 0u);
     } else {
       ptx::mbar_arrive(sm_empty + 8u * s_cur);
     }
@@ -841,9 +951,9 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
   const bool aligned16 =
       ((reinterpret_cast<uintptr_t>(XC) | reinterpret_cast<uintptr_t>(idx) |
         reinterpret_cast<uintptr_t>(Q) | reinterpret_cast<uintptr_t>(valid)) & 15) == 0;
+#if FRODO_RAYS_WS
   if (prm.mode == FRODO_GN_RAYS && XC != nullptr && (N % 16) == 0 && aligned16) {
     static bool attr_set = false;
-#if FRODO_RAYS_WS
     const size_t smem = (size_t)kWsSmemBytes;
     if (!attr_set) {
       FRODO_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_rays_ws_kernel,
@@ -855,21 +965,43 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
         prm, Twc, reinterpret_cast<const float4*>(XC),
         reinterpret_cast<const float4*>(XC) + (size_t)K * N, ii_row, jj_row, idx, valid, Q, N, ppc,
         nchunks, nitems, partials, tickets, edge_blocks, done);
-#else
-    const size_t smem = (size_t)kRaysSmemBytes;
-    if (!attr_set) {
-      FRODO_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_rays_packed_kernel,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr_set = true;
-    }
-    gn_accumulate_rays_packed_kernel<<<grid, kRaysThreads, smem, s>>>(
-        prm, Twc, reinterpret_cast<const float4*>(XC),
-        reinterpret_cast<const float4*>(XC) + (size_t)K * N, ii_row, jj_row, idx, valid, Q, N, ppc,
-        partials, tickets, edge_blocks, done);
-#endif
     FRODO_CUDA_TRY(cudaGetLastError());
     return FRODO_OK;
   }
+#else
+  // packed fast path (all three modes): needs the repacked pointmaps and 16-byte alignment;
+  // calib additionally needs N < 2^32 target pixels, which N as an int guarantees
+  if (XC != nullptr && (N % 16) == 0 && aligned16 &&
+      (prm.mode != FRODO_GN_CALIB || Kmat != nullptr)) {
+    static bool attr_set = false;
+    const size_t smem = (size_t)kRaysSmemBytes;
+    if (!attr_set) {
+      FRODO_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_packed_kernel<FRODO_GN_RAYS>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      FRODO_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_packed_kernel<FRODO_GN_POINTS>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      FRODO_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_packed_kernel<FRODO_GN_CALIB>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_set = true;
+    }
+    const float4* xc = reinterpret_cast<const float4*>(XC);
+    const float4* xp = xc + (size_t)K * N;
+    if (prm.mode == FRODO_GN_RAYS)
+      gn_accumulate_packed_kernel<FRODO_GN_RAYS><<<grid, kRaysThreads, smem, s>>>(
+          prm, Twc, Kmat, xc, xp, ii_row, jj_row, idx, valid, Q, N, ppc, partials, tickets,
+          edge_blocks, done);
+    else if (prm.mode == FRODO_GN_POINTS)
+      gn_accumulate_packed_kernel<FRODO_GN_POINTS><<<grid, kRaysThreads, smem, s>>>(
+          prm, Twc, Kmat, xc, xp, ii_row, jj_row, idx, valid, Q, N, ppc, partials, tickets,
+          edge_blocks, done);
+    else
+      gn_accumulate_packed_kernel<FRODO_GN_CALIB><<<grid, kRaysThreads, smem, s>>>(
+          prm, Twc, Kmat, xc, xp, ii_row, jj_row, idx, valid, Q, N, ppc, partials, tickets,
+          edge_blocks, done);
+    FRODO_CUDA_TRY(cudaGetLastError());
+    return FRODO_OK;
+  }
+#endif
   switch (prm.mode) {
     case FRODO_GN_RAYS:
       gn_accumulate_kernel<FRODO_GN_RAYS><<<grid, kThreads, 0, s>>>(

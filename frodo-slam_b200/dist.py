@@ -51,9 +51,9 @@ class ShardedGaussNewton:
                                                None, _stream()))
             self.ii_row = ii_row[lo:hi].contiguous()
             self.jj_row = jj_row[lo:hi].contiguous()
-            # rays fast path: pointmaps repacked as float4 inside the workspace, once per solve
+            # packed fast path: pointmaps repacked inside the workspace, once per solve
             self.xc = None
-            if params.mode == _lib.GN_RAYS and self.N % 16 == 0 and self.E_local > 0:
+            if self.N % 16 == 0 and self.E_local > 0:
                 off = lib.frodo_gn_workspace_packed_offset(self.num_kf, max(self.E_local, 1), self.N)
                 self.xc = ctypes.c_void_p(self.ws.data_ptr() + off)
 
