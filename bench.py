@@ -54,24 +54,73 @@ class ClockSampler:
 
     def __init__(self, index=0):
         self.rows, self.proc, self.index = [], None, index
+        self.nvml_rows, self._stop, self._thread = [], threading.Event(), None
+
+    # NVML is polled from a thread every 5 ms (the timed region of a default run is tens of
+    # milliseconds: an `nvidia-smi -lms` child is too slow to start and to tick); nvidia-smi is
+    # the fallback when the NVML binding cannot be used.
+    def _nvml_loop(self, h, nv):
+        bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown,
+                "hw_thermal_slowdown": nv.nvmlClocksEventReasonHwThermalSlowdown,
+                "sw_thermal_slowdown": nv.nvmlClocksEventReasonSwThermalSlowdown,
+                "sw_power_cap": nv.nvmlClocksEventReasonSwPowerCap}
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        while not self._stop.is_set():
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                self.nvml_rows.append((float(sm), float(mx), [n for n, b in bits.items() if r & b]))
+            except Exception:
+                break
+            time.sleep(0.005)
 
     def start(self):
         try:
+            import pynvml as nv
+            nv.nvmlInit()
+            try:
+                uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+                h = nv.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:
+                h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+            self._thread = threading.Thread(target=self._nvml_loop, args=(h, nv), daemon=True)
+            self._thread.start()
+            return
+        except Exception:
+            self._thread = None
+        try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+                 "-i", str(self.index), "-lms", "20"], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=self._read, daemon=True).start()
+            t0 = time.time()
+            while not self.rows and time.time() - t0 < 5.0:  # wait for the first tick
+                time.sleep(0.02)
         except Exception:
             self.proc = None
+
+    def mark(self):
+        """Start of the timed region: earlier samples (warm-up) are dropped."""
+        self.nvml_rows.clear()
+        self.rows.clear()
 
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append([x.strip() for x in line.split(",")])
 
     def stop(self):
+        if self._thread is not None:
+            self._stop.set()
+            self._thread.join(timeout=1.0)
+            sm = [r[0] for r in self.nvml_rows]
+            reasons = sorted({n for r in self.nvml_rows for n in r[2]})
+            return {"sm_mhz": float(np.median(sm)) if sm else None,
+                    "sm_max_mhz": self.nvml_rows[0][1] if sm else None, "reasons": reasons,
+                    "samples": len(sm), "source": "nvml, 5 ms period"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.05)
         self.proc.terminate()
         sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
         mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
@@ -80,7 +129,7 @@ class ClockSampler:
                    if any(len(r) >= 6 and r[2 + k].lower() == "active" for r in self.rows)]
         return {"sm_mhz": float(np.median(sm)) if sm else None,
                 "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(sm)}
+                "samples": len(sm), "source": "nvidia-smi -lms 20"}
 
 
 def dist_env():
@@ -97,7 +146,7 @@ def build_graph(device, num_kf_cfg="loop64"):
     return K, g
 
 
-def timed_steps(fn, steps, warmup, barrier=None):
+def timed_steps(fn, steps, warmup, barrier=None, on_start=None):
     """W warm-up calls, then K calls bracketed by barrier + synchronize; CUDA-event time (ms)."""
     for _ in range(warmup):
         fn()
@@ -105,6 +154,8 @@ def timed_steps(fn, steps, warmup, barrier=None):
     if barrier:
         barrier()
     torch.cuda.synchronize()
+    if on_start:
+        on_start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(steps):
@@ -288,7 +339,8 @@ def main_ours(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ms = timed_steps(step, args.steps, args.warmup, barrier)
+    ms = timed_steps(step, args.steps, args.warmup, barrier,
+                     on_start=sampler.mark if rank == 0 else None)
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

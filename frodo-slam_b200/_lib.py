@@ -28,6 +28,13 @@ class MatchParams(ctypes.Structure):
                 ("dist_thresh", c_float), ("radius", c_int), ("dilation_max", c_int),
                 ("ft_matching_threshold", c_float)]
 
+class TrackParams(ctypes.Structure):
+    """struct frodo_track_params (include/frodo_b200.h)."""
+    _fields_ = [("mode", c_int), ("sigma_a", c_float), ("sigma_b", c_float), ("huber", c_float),
+                ("max_iters", c_int), ("rel_error", c_float), ("delta_norm", c_float),
+                ("height", c_int), ("width", c_int), ("pixel_border", c_int), ("z_eps", c_float)]
+
+
 # name -> (restype, argtypes); kept in sync with include/frodo_b200.h (tests check this)
 SIGNATURES = {
     "frodo_version": (c_int, []),
@@ -62,6 +69,9 @@ SIGNATURES = {
                                      [c_int, c_int, c_void_p, c_float, c_float, c_float] +
                                      [c_int] * 5 + [c_float, c_void_p, c_void_p, c_void_p,
                                                     c_size_t, c_void_p]),
+    "frodo_track_workspace_bytes": (c_size_t, [c_int]),
+    "frodo_track_pose": (c_int, [ctypes.POINTER(TrackParams)] + [c_void_p] * 10 + [c_int] +
+                         [c_void_p] * 5 + [c_size_t, c_void_p]),
 }
 
 _lib = None

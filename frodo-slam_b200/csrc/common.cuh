@@ -54,4 +54,12 @@ int launch_match_finish(const int64_t* p1, const void* scores, bool scores_f16,
                         const uint8_t* valid_in, float threshold, int64_t* idx, uint8_t* valid,
                         int B, int N, int W, cudaStream_t s);
 
+
+size_t track_workspace_bytes(int N);
+int launch_track_pose(const frodo_track_params& prm, const float* Xf, const int64_t* idx,
+                      const float* Xk, const float* Qk, const uint8_t* valid, const float* meas,
+                      const uint8_t* valid_meas, const float* Kmat, const float* T_WCf,
+                      const float* T_WCk, int N, float* T_WCf_out, float* T_CkCf_out,
+                      int32_t* info, double* costs, void* workspace, cudaStream_t s);
+
 }  // namespace frodo

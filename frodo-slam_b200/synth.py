@@ -281,3 +281,41 @@ def odometry_edges(g, seed=7, noise_t=2e-4, noise_r=2e-4, skip_prior=(2,), devic
             s_bar[k] = 0.0
     dev = device if device is not None else g["Twc"].device
     return dict(odom_ii=i.to(dev), odom_jj=j.to(dev), Tij=Tij.contiguous().to(dev), s_bar=s_bar)
+
+
+# ------------------------------------------------------------------ tracker
+
+# config/base.yaml:18-35 of the reference (the `tracking` section)
+TRACK_PARAMS = dict(max_iters=50, C_conf=0.0, Q_conf=1.5, rel_error=1e-3, delta_norm=1e-3,
+                    huber=1.345, sigma_ray=0.003, sigma_dist=10.0, sigma_pixel=1.0,
+                    sigma_depth=10.0, pixel_border=-10, depth_eps=1e-6)
+
+
+def tracking_case(H, W, seed=1, device="cpu", pose_noise=0.01, valid_frac=0.8, jitter_px=1.0):
+    """One frame tracked against one keyframe (tracker.py:160-300): the inputs of
+    FrameTracker.opt_pose_ray_dist_sim3 / opt_pose_calib_sim3 at FULL size (no compaction).
+
+    Keyframe = keyframe 0 and frame = keyframe 1 of a two-keyframe graph; the directed edge
+    (i = frame, j = keyframe) carries idx_f2k (for keyframe pixel n, its pixel in the frame),
+    valid_match and Q.  Returns dict: Xf_all [N,3] (the frame's own pointmap), idx_f2k [N] i64,
+    Xf [N,3] = Xf_all[idx_f2k] (tracker.py:395), Xk [N,3], Cf, Ck [N,1], Qk [N,1],
+    valid [N,1] bool = valid_match & Q > Q_conf & C > C_conf (tracker.py:199-204),
+    T_WCf, T_WCk [1,8] (the frame's pose perturbed), T_WCf_true, K [3,3], H, W."""
+    g = keyframe_graph(2, H, W, [(0, 1)], seed=seed, device=device, pose_noise=pose_noise,
+                       valid_frac=valid_frac, jitter_px=jitter_px)
+    # directed edges are [(0,1), (1,0)]; edge 1 has i = 1 (frame), j = 0 (keyframe):
+    # idx[1, n] = pixel of the FRAME matched to keyframe pixel n
+    e = 1
+    idx = g["idx_ii2jj"][e].contiguous()
+    Xf_all = g["Xs"][1].contiguous()
+    Xk = g["Xs"][0].contiguous()
+    Cf = g["Cs"][1][idx].contiguous()
+    Ck = g["Cs"][0].contiguous()
+    Qk = g["Q"][e].contiguous()
+    tp = TRACK_PARAMS
+    valid = (g["valid_match"][e] & (Qk > tp["Q_conf"]) & (Cf > tp["C_conf"])
+             & (Ck > tp["C_conf"])).contiguous()
+    return dict(Xf_all=Xf_all, idx_f2k=idx, Xf=Xf_all[idx].contiguous(), Xk=Xk, Cf=Cf, Ck=Ck,
+                Qk=Qk, valid=valid, T_WCf=g["Twc"][1:2].contiguous(),
+                T_WCk=g["Twc"][0:1].contiguous(), T_WCf_true=g["Twc_true"][1:2].contiguous(),
+                K=g["K"], H=H, W=W)

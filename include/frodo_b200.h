@@ -17,6 +17,9 @@
  *   mast3r_slam/backend/src/gn.cpp:3-26      gauss_newton_points
  *   mast3r_slam/backend/src/gn.cpp:90-118    gauss_newton_calib
  *   mast3r_slam/backend/include/gn.h         (*_cuda launchers)
+ *   mast3r_slam/backend/src/gn.cpp:29-62     gauss_newton_rays_odom
+ *   mast3r_slam/matching.py:8-110            match() and its helpers (Python in the reference)
+ *   mast3r_slam/tracker.py:397-517           the tracker's pose solve (Python in the reference)
  */
 #ifndef FRODO_B200_H
 #define FRODO_B200_H
@@ -221,6 +224,48 @@ int frodo_gauss_newton_rays_odom(const frodo_gn_params* params, float* Twc, cons
                                  int K, int N, int E, int num_fix, int max_iter,
                                  float delta_thresh, float* dx, int32_t* info, void* workspace,
                                  size_t workspace_bytes, frodo_stream_t stream);
+
+/* ---- the tracker's frame-to-keyframe pose solve -----------------------
+ * FrameTracker.opt_pose_ray_dist_sim3 / opt_pose_calib_sim3 / solve, mast3r_slam/tracker.py:397-517
+ * (+ geometry.py:17-104, nonlinear_optimizer.py:4-33): up to max_iters Gauss-Newton steps on the
+ * relative pose T_CkCf = T_WCk^-1 T_WCf with Huber weights, stopped on device by the reference's
+ * test (relative cost decrease < rel_error or ||tau|| < delta_norm).  One persistent cooperative
+ * kernel, no host synchronisation.
+ *   mode FRODO_GN_RAYS : residual [ray(3), distance(1)] of T_CkCf * Xf against Xk (sigma_a =
+ *                        sigma_ray, sigma_b = sigma_dist).
+ *   mode FRODO_GN_CALIB: residual [u, v, log z] of the pinhole projection of T_CkCf * Xf against
+ *                        meas_k [N,3] (sigma_a = sigma_pixel, sigma_b = sigma_depth); needs Kmat
+ *                        [3,3] (device), valid_meas_k [N] u8, height / width / pixel_border / z_eps.
+ *   Xf [*,3] f32: the frame's points; row idx_f2k[n] is matched to keyframe point n (idx_f2k
+ *     [N] i64, NULL = identity, i.e. Xf already gathered as tracker.py:395 does).
+ *   Xk [N,3] f32 (rays only), Qk [N] f32, valid [N] u8: FULL-size arrays; the reference compacts
+ *     by `valid` (tracker.py:293-295) or multiplies the information by it (:471-472), here a
+ *     point with valid == 0 has zero weight.
+ *   T_WCf, T_WCk [8] f32 device (t, q_xyzw, s).  Outputs (device): T_WCf_new [8] = T_WCk * T_CkCf,
+ *     T_CkCf [8], info int32[2] = {iterations executed, 1 if the 7x7 system was not positive
+ *     definite (the reference's "Cholesky failed")}, costs f64 [max_iters] (may be NULL).
+ *   workspace: frodo_track_workspace_bytes(N) bytes. */
+typedef struct frodo_track_params {
+  int mode;
+  float sigma_a;
+  float sigma_b;
+  float huber; /* 1.345 */
+  int max_iters;
+  float rel_error;
+  float delta_norm;
+  int height; /* calib only */
+  int width;
+  int pixel_border;
+  float z_eps;
+} frodo_track_params;
+
+size_t frodo_track_workspace_bytes(int N);
+int frodo_track_pose(const frodo_track_params* params, const float* Xf, const int64_t* idx_f2k,
+                     const float* Xk, const float* Qk, const uint8_t* valid, const float* meas_k,
+                     const uint8_t* valid_meas_k, const float* Kmat, const float* T_WCf,
+                     const float* T_WCk, int N, float* T_WCf_new, float* T_CkCf, int32_t* info,
+                     double* costs, void* workspace, size_t workspace_bytes,
+                     frodo_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -375,3 +375,254 @@ def match(X11, X21, D11, D21, idx_1_to_2_init=None, max_iter=10, lambda_init=1e-
     D21h = np.asarray(D21).astype(np.float16).reshape(b, h * w, -1)
     p1, scores = refine_matches(D11h, D21h, p1, radius, dilation_max)
     return match_finish(p1, scores, valid, w, ft_matching_threshold)
+
+
+# ----------------------------------------------------------------------------------------
+# The tracker's frame-to-keyframe pose solve: tracker.py:397-517 with
+# geometry.py:17-34 (point_to_ray_dist), :45-52 (act_Sim3), :63-104 (project_calib) and
+# nonlinear_optimizer.py:4-33 (check_convergence, huber).  The reference runs it as ~15 PyTorch
+# kernels per iteration on fp32 tensors with lietorch.Sim3 group operations (lietorch is an
+# unpinned git dependency, absent from /root/reference: its Sim3 act / inv / mul / retr are
+# restated here from the published formulas, the same ones gn_kernels.cu:219-314,341-455
+# carries; Exp goes through the oracle's pose_retr, pinned to the reference kernel).
+# numpy fp32, vectorised over the points.  Pinned against the reference's own tracker.py run
+# on a stub lietorch: tests/golden/make_golden_track.py -> golden_track.npz.
+# ----------------------------------------------------------------------------------------
+
+def _f32(a):
+    return np.asarray(a, dtype=np.float32)
+
+
+def sim3_act(T, X):
+    """lietorch Sim3.act: s R x + t.  T [8] = [t, q_xyzw, s], X [N,3]."""
+    T = _f32(T).reshape(8)
+    X = _f32(X)
+    q = T[3:6]
+    uv = np.float32(2.0) * np.cross(q[None, :], X).astype(np.float32)
+    Y = X + T[6] * uv + np.cross(q[None, :], uv).astype(np.float32)
+    return (T[7] * Y + T[None, 0:3]).astype(np.float32)
+
+
+def _quat_mul(a, b):
+    return np.array([a[3] * b[0] + a[0] * b[3] + a[1] * b[2] - a[2] * b[1],
+                     a[3] * b[1] - a[0] * b[2] + a[1] * b[3] + a[2] * b[0],
+                     a[3] * b[2] + a[0] * b[1] - a[1] * b[0] + a[2] * b[3],
+                     a[3] * b[3] - a[0] * b[0] - a[1] * b[1] - a[2] * b[2]], dtype=np.float32)
+
+
+def sim3_inv(T):
+    """lietorch Sim3.inv: [ -s^-1 R^T t, q^-1, s^-1 ]."""
+    T = _f32(T).reshape(8)
+    qi = np.array([-T[3], -T[4], -T[5], T[6]], np.float32)
+    si = np.float32(1.0) / T[7]
+    Ti = np.zeros(8, np.float32)
+    Ti[3:7] = qi
+    Ti[7] = 1.0
+    rt = sim3_act(Ti, T[None, 0:3])[0]
+    Ti[0:3] = -si * rt
+    Ti[7] = si
+    return Ti
+
+
+def sim3_mul(A, B):
+    """lietorch Sim3 product A * B: [ s_a R_a t_b + t_a, q_a q_b, s_a s_b ]."""
+    A = _f32(A).reshape(8)
+    B = _f32(B).reshape(8)
+    out = np.zeros(8, np.float32)
+    out[0:3] = sim3_act(A, B[None, 0:3])[0]
+    out[3:7] = _quat_mul(A[3:7], B[3:7])
+    out[7] = A[7] * B[7]
+    return out
+
+
+def sim3_retr(T, tau):
+    """lietorch Sim3.retr: Exp(tau) * T (expSim3 / retrSim3, gn_kernels.cu:365-455)."""
+    return pose_retr(_f32(T).reshape(1, 8), _f32(tau).reshape(1, 7), 0)[0]
+
+
+def _huber_w(r, k):
+    a = np.abs(r)
+    with np.errstate(divide="ignore"):
+        return np.where(a < k, np.float32(1.0), np.float32(k) / a).astype(np.float32)
+
+
+def _track_loop(T_CkCf, T_WCk, step_fn, huber_k, max_iters, rel_error, delta_norm):
+    """The iteration of tracker.py:433-460 / :477-512 with FrameTracker.solve (:397-412)."""
+    old_cost = float("inf")
+    costs = []
+    iters = 0
+    status = 0
+    for step in range(max_iters):
+        sqrt_info, r, J = step_fn(T_CkCf)
+        whitened = sqrt_info * r
+        rsi = (sqrt_info * np.sqrt(_huber_w(whitened, huber_k))).astype(np.float32)
+        mdim = J.shape[-1]
+        A = (rsi[..., None] * J).reshape(-1, mdim).astype(np.float32)
+        b = (rsi * r).reshape(-1, 1).astype(np.float32)
+        H = (A.T @ A).astype(np.float32)
+        g = (-A.T @ b).astype(np.float32)
+        cost = 0.5 * float((b.T @ b)[0, 0])
+        try:
+            L = np.linalg.cholesky(H.astype(np.float64))
+        except np.linalg.LinAlgError:
+            status = 1  # torch.linalg.cholesky raises; track() reports "Cholesky failed"
+            break
+        tau = np.linalg.solve(L.T, np.linalg.solve(L, g.astype(np.float64))).astype(np.float32)
+        T_CkCf = sim3_retr(T_CkCf, tau.reshape(7))
+        costs.append(cost)
+        iters = step + 1
+        # check_convergence, nonlinear_optimizer.py:4-25 (old_cost = inf on step 0 -> nan -> False)
+        with np.errstate(invalid="ignore"):
+            rel_dec = abs(float(np.float64(old_cost - cost) / np.float64(old_cost))) \
+                if np.isfinite(old_cost) else float("nan")
+        dn = float(np.linalg.norm(tau))
+        if rel_dec < rel_error or dn < delta_norm:
+            break
+        old_cost = cost
+    T_WCf = sim3_mul(T_WCk, T_CkCf)
+    return dict(T_WCf=T_WCf, T_CkCf=T_CkCf, iters=iters, costs=np.array(costs, np.float64),
+                status=status)
+
+
+def _act_jac(T, Xf):
+    """act_Sim3 with jacobian, geometry.py:45-52: [I, -[p]x, p]."""
+    P = sim3_act(T, Xf)
+    n = P.shape[0]
+    J = np.zeros((n, 3, 7), np.float32)
+    J[:, 0, 0] = J[:, 1, 1] = J[:, 2, 2] = 1.0
+    x, y, z = P[:, 0], P[:, 1], P[:, 2]
+    J[:, 0, 4] = z; J[:, 0, 5] = -y
+    J[:, 1, 3] = -z; J[:, 1, 5] = x
+    J[:, 2, 3] = y; J[:, 2, 4] = -x
+    J[:, :, 6] = P
+    return P, J
+
+
+def _ray_dist(X, jacobian):
+    """point_to_ray_dist, geometry.py:17-34."""
+    d = np.linalg.norm(X, axis=-1, keepdims=True).astype(np.float32)
+    d_inv = (np.float32(1.0) / d).astype(np.float32)
+    r = d_inv * X
+    rd = np.concatenate((r, d), axis=-1).astype(np.float32)
+    if not jacobian:
+        return rd
+    d_inv_2 = d_inv ** 2
+    I = np.eye(3, dtype=np.float32)[None]
+    dr = d_inv[..., None] * (I - d_inv_2[..., None] * (X[:, :, None] * X[:, None, :]))
+    drd = np.concatenate((dr, r[:, None, :]), axis=-2).astype(np.float32)
+    return rd, drd
+
+
+def track_pose_rays(Xf, Xk, T_WCf, T_WCk, Qk, valid, sigma_ray=0.003, sigma_dist=10.0,
+                    huber=1.345, max_iters=50, rel_error=1e-3, delta_norm=1e-3, idx_f2k=None):
+    """FrameTracker.opt_pose_ray_dist_sim3, tracker.py:414-465, on FULL-size arrays: the caller's
+    compaction by valid_opt (tracker.py:293-295) happens here.  Xf [N,3] is the frame's pointmap
+    (already gathered by idx_f2k, or gathered here when idx_f2k is given, tracker.py:395),
+    Xk [N,3] the keyframe's, Qk [N,1], valid [N,1] bool, poses [8]."""
+    Xf = _f32(Xf).reshape(-1, 3)
+    if idx_f2k is not None:
+        Xf = Xf[np.asarray(idx_f2k).reshape(-1)]
+    m = np.asarray(valid).reshape(-1).astype(bool)
+    Xf = Xf[m]
+    Xk = _f32(Xk).reshape(-1, 3)[m]
+    Qk = _f32(Qk).reshape(-1, 1)[m]
+    sq = np.sqrt(Qk).astype(np.float32)
+    si_ray = (np.float32(1.0 / sigma_ray) * sq).astype(np.float32)
+    si_dist = (np.float32(1.0 / sigma_dist) * sq).astype(np.float32)
+    sqrt_info = np.concatenate((np.repeat(si_ray, 3, axis=1), si_dist), axis=1)
+    T_CkCf = sim3_mul(sim3_inv(T_WCk), T_WCf)
+    rd_k = _ray_dist(Xk, False)
+
+    def step_fn(T):
+        P, dP = _act_jac(T, Xf)
+        rd_f, drd = _ray_dist(P, True)
+        r = rd_k - rd_f
+        J = -(drd @ dP)
+        return sqrt_info, r, J.astype(np.float32)
+
+    return _track_loop(T_CkCf, T_WCk, step_fn, huber, max_iters, rel_error, delta_norm)
+
+
+def track_pose_calib(Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K, img_size,
+                     sigma_pixel=1.0, sigma_depth=10.0, pixel_border=-10, depth_eps=1e-6,
+                     huber=1.345, max_iters=50, rel_error=1e-3, delta_norm=1e-3, idx_f2k=None):
+    """FrameTracker.opt_pose_calib_sim3, tracker.py:467-517 (+ project_calib, geometry.py:63-104).
+    All arrays full size; `valid` multiplies the information (tracker.py:471-472)."""
+    Xf = _f32(Xf).reshape(-1, 3)
+    if idx_f2k is not None:
+        Xf = Xf[np.asarray(idx_f2k).reshape(-1)]
+    v = np.asarray(valid).reshape(-1, 1).astype(np.float32)
+    Qk = _f32(Qk).reshape(-1, 1)
+    meas_k = _f32(meas_k).reshape(-1, 3)
+    vmk = np.asarray(valid_meas_k).reshape(-1, 1).astype(bool)
+    K = _f32(K).reshape(3, 3)
+    fx, fy, cx, cy = K[0, 0], K[1, 1], K[0, 2], K[1, 2]
+    sq = np.sqrt(Qk).astype(np.float32)
+    si_p = (np.float32(1.0 / sigma_pixel) * v * sq).astype(np.float32)
+    si_d = (np.float32(1.0 / sigma_depth) * v * sq).astype(np.float32)
+    sqrt_info = np.concatenate((np.repeat(si_p, 2, axis=1), si_d), axis=1)
+    T_CkCf = sim3_mul(sim3_inv(T_WCk), T_WCf)
+    h, w = img_size
+
+    def step_fn(T):
+        P, dP = _act_jac(T, Xf)
+        x, y, z = P[:, 0:1], P[:, 1:2], P[:, 2:3]
+        with np.errstate(divide="ignore", invalid="ignore"):
+            p = (P @ K.T).astype(np.float32)
+            p = (p / p[:, 2:3])[:, :2]
+            u, vv = p[:, 0:1], p[:, 1:2]
+            valid_u = (u > pixel_border) & (u < w - 1 - pixel_border)
+            valid_v = (vv > pixel_border) & (vv < h - 1 - pixel_border)
+            valid_z = z > depth_eps
+            vproj = valid_u & valid_v & valid_z
+            logz = np.log(z).astype(np.float32)
+            logz[~valid_z] = 0.0
+            pz = np.concatenate((p, logz), axis=-1)
+            z_inv = (np.float32(1.0) / z[:, 0]).astype(np.float32)
+            d = np.zeros((P.shape[0], 3, 3), np.float32)
+            d[:, 0, 0] = fx
+            d[:, 1, 1] = fy
+            d[:, 0, 2] = -fx * x[:, 0] * z_inv
+            d[:, 1, 2] = -fy * y[:, 0] * z_inv
+            d *= z_inv[:, None, None]
+            d[:, 2, 2] = z_inv
+            valid2 = vproj & vmk
+            si2 = np.where(valid2, sqrt_info, np.float32(0.0)).astype(np.float32)
+            r = (meas_k - pz).astype(np.float32)
+            J = -(d @ dP)
+            # rows with zero information contribute 0 in the reference unless they hold inf / nan;
+            # the synthetic inputs keep them finite, and the masks below make that explicit
+            bad = ~np.isfinite(r).all(axis=1) | ~np.isfinite(J).all(axis=(1, 2))
+            r[bad] = 0.0
+            J[bad] = 0.0
+        return si2, r, J.astype(np.float32)
+
+    return _track_loop(T_CkCf, T_WCk, step_fn, huber, max_iters, rel_error, delta_norm)
+
+
+def track_meas_calib(Xf, Xk, K, img_size, depth_eps=1e-6):
+    """The calibrated branch of FrameTracker.get_points_poses, tracker.py:383-393 (+
+    constrain_points_to_ray / backproject / get_pixel_coords, geometry.py:37-42,107-124): both
+    pointmaps are re-projected onto their own pixel rays at their depth; the measurement of the
+    keyframe is (u, v, log z) with invalid-depth rows zeroed."""
+    h, w = img_size
+    K = _f32(K).reshape(3, 3)
+    vv, uu = np.meshgrid(np.arange(h, dtype=np.float32), np.arange(w, dtype=np.float32),
+                         indexing="ij")
+    uv = np.stack((uu, vv), axis=-1).reshape(-1, 2)
+
+    def constrain(X):
+        X = _f32(X).reshape(-1, 3)
+        z = X[:, 2:3]
+        t1 = (uv[:, 0] - K[0, 2]) / K[0, 0]
+        t2 = (uv[:, 1] - K[1, 2]) / K[1, 1]
+        d = np.stack((t1, t2, np.ones_like(t1)), axis=-1).astype(np.float32)
+        return (z * d).astype(np.float32)
+
+    Xf2 = constrain(Xf)
+    Xk2 = constrain(Xk)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        meas = np.concatenate((uv, np.log(Xk2[:, 2:3])), axis=-1).astype(np.float32)
+    vmk = Xk2[:, 2:3] > depth_eps
+    meas[~np.repeat(vmk, 3, axis=1)] = 0.0
+    return Xf2, Xk2, meas, vmk
