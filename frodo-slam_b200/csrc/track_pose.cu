@@ -27,7 +27,7 @@ namespace frodo {
 
 namespace {
 
-constexpr int kTrkThreads = 256;
+constexpr int kTrkThreads = 512;
 constexpr int kTrkWarps = kTrkThreads / 32;
 constexpr int kRec = 8;        // floats per point record
 constexpr int kSums = 36;      // 28 (upper triangle of H) + 7 (v) + 1 (cost)
@@ -60,7 +60,7 @@ struct TrackArgs {
 
 __device__ __forceinline__ float huber_w(float r, float k) {
   const float a = fabsf(r);
-  return a < k ? 1.0f : k / a;
+  return a < k ? 1.0f : __fdividef(k, a);
 }
 
 // S (28 upper-triangular entries, row-major) += w x x^T, v += (w e) x over the entries in MASK.
@@ -100,8 +100,8 @@ __device__ __forceinline__ void point(const TrackArgs& a, const float* T, const 
   if (MODE == FRODO_GN_RAYS) {
     const float sq = rec[7];
     const float n2 = P[0] * P[0] + P[1] * P[1] + P[2] * P[2];
-    const float d = sqrtf(n2);
-    const float d_inv = 1.0f / d;
+    const float d_inv = rsqrtf(n2);
+    const float d = n2 * d_inv;
     const float r0 = P[0] * d_inv, r1 = P[1] * d_inv, r2 = P[2] * d_inv;
     const float e0 = r0 - rec[3], e1 = r1 - rec[4], e2 = r2 - rec[5], e3 = d - rec[6];
     const float sw_r = a.sa_inv * sq, sw_d = a.sb_inv * sq;
@@ -128,7 +128,7 @@ __device__ __forceinline__ void point(const TrackArgs& a, const float* T, const 
     add_row<0x47u>(S, v, cost, x, w3, e3);
   } else {  // calib: project_calib, geometry.py:63-104
     const bool valid_z = P[2] > a.z_eps;
-    const float zinv = valid_z ? 1.0f / P[2] : 0.0f;
+    const float zinv = valid_z ? __fdividef(1.0f, P[2]) : 0.0f;
     const float logz = valid_z ? logf(P[2]) : 0.0f;
     const float xz = P[0] * zinv, yz = P[1] * zinv;
     const float u = fmaf(a.fx, xz, a.cx);
@@ -176,34 +176,47 @@ __device__ void compose_pose(const float* A, const float* B, float* C) {
 
 // 7x7 fp64 Cholesky solve of H tau = -v from the 36 sums; false if H is not positive definite
 // (torch.linalg.cholesky raises in the reference, tracker.py:407; track() reports failure).
-__device__ bool solve7(const double* sums, double* tau) {
-  double L[7][7];
-  int l = 0;
-  for (int n = 0; n < 7; ++n)
-    for (int m = n; m < 7; ++m) L[m][n] = sums[l++];
+__device__ __forceinline__ bool solve7(const double* sums, double* tau) {
+  double L[7][7];  // fully unrolled below: lives in registers
+  {
+    int l = 0;
+#pragma unroll
+    for (int n = 0; n < 7; ++n)
+#pragma unroll
+      for (int m = n; m < 7; ++m) L[m][n] = sums[l++];
+  }
+  bool ok = true;
+#pragma unroll
   for (int j = 0; j < 7; ++j) {
     double d = L[j][j];
-    for (int k = 0; k < j; ++k) d -= L[j][k] * L[j][k];
-    if (!(d > 0.0) || !isfinite(d)) return false;
-    const double s = sqrt(d);
-    L[j][j] = s;
-    const double inv = 1.0 / s;
+#pragma unroll
+    for (int k = 0; k < j; ++k) d = fma(-L[j][k], L[j][k], d);
+    ok = ok && (d > 0.0) && isfinite(d);
+    const double inv = rsqrt(d);
+    L[j][j] = inv;  // the diagonal holds 1 / l_jj
+#pragma unroll
     for (int i = j + 1; i < 7; ++i) {
       double t = L[i][j];
-      for (int k = 0; k < j; ++k) t -= L[i][k] * L[j][k];
+#pragma unroll
+      for (int k = 0; k < j; ++k) t = fma(-L[i][k], L[j][k], t);
       L[i][j] = t * inv;
     }
   }
+  if (!ok) return false;
   double y[7];
+#pragma unroll
   for (int i = 0; i < 7; ++i) {
     double t = -sums[28 + i];
-    for (int k = 0; k < i; ++k) t -= L[i][k] * y[k];
-    y[i] = t / L[i][i];
+#pragma unroll
+    for (int k = 0; k < i; ++k) t = fma(-L[i][k], y[k], t);
+    y[i] = t * L[i][i];
   }
+#pragma unroll
   for (int i = 6; i >= 0; --i) {
     double t = y[i];
-    for (int k = i + 1; k < 7; ++k) t -= L[k][i] * tau[k];
-    tau[i] = t / L[i][i];
+#pragma unroll
+    for (int k = i + 1; k < 7; ++k) t = fma(-L[k][i], tau[k], t);
+    tau[i] = t * L[i][i];
   }
   return true;
 }
@@ -303,13 +316,32 @@ __global__ void __launch_bounds__(kTrkThreads, 1) track_pose_kernel(const TrackA
       }
       point<MODE>(a, T, r, S, v, cost);
     }
-    // ---- CTA reduction: warp butterflies, then fp64 across the warps ---------------------
+    // ---- CTA reduction: warp reduce-scatter (lane m ends with the warp total of entry m,
+    // 31 exchanges for 32 entries) + butterflies for the last 4, then fp64 across the warps --
+    {
+      float r32[32];
 #pragma unroll
-    for (int l = 0; l < kSums; ++l) {
-      float x = l < 28 ? S[l] : (l < 35 ? v[l - 28] : cost);
+      for (int l = 0; l < 28; ++l) r32[l] = S[l];
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-      if (lane == 0) warp_part[warp][l] = x;
+      for (int l = 0; l < 4; ++l) r32[28 + l] = v[l];
+#pragma unroll
+      for (int half = 16; half >= 1; half >>= 1) {
+        const bool up = (lane & half) != 0;
+#pragma unroll
+        for (int i = 0; i < half; ++i) {
+          const float send = up ? r32[i] : r32[i + half];
+          const float keep = up ? r32[i + half] : r32[i];
+          r32[i] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+        }
+      }
+      warp_part[warp][lane] = r32[0];
+#pragma unroll
+      for (int l = 32; l < kSums; ++l) {
+        float x = l < 35 ? v[l - 28] : cost;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        if (lane == 0) warp_part[warp][l] = x;
+      }
     }
     __syncthreads();
     double* part = a.partials + (size_t)(it & 1) * G * kSums;

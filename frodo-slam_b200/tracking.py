@@ -109,10 +109,12 @@ def track_pose(mode, Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k=None, valid_meas_k=
     Tk = _pose_tensor(T_WCk, "T_WCk", dev)
     lib = _lib.load()
     with torch.cuda.device(dev):
-        out_f = torch.empty(8, dtype=torch.float32, device=dev)
-        out_rel = torch.empty(8, dtype=torch.float32, device=dev)
-        info = torch.zeros(2, dtype=torch.int32, device=dev)
-        costs = torch.zeros(max(prm.max_iters, 1), dtype=torch.float64, device=dev)
+        # one allocation for the outputs (the kernel writes poses and info unconditionally and
+        # costs[:iterations]), one for the workspace; nothing needs zeroing by the caller
+        outs = torch.empty(max(prm.max_iters, 1) + 9, dtype=torch.float64, device=dev)
+        costs = outs[9:]
+        out_f, out_rel = outs[0:4].view(torch.float32), outs[4:8].view(torch.float32)
+        info = outs[8:9].view(torch.int32)
         nbytes = lib.frodo_track_workspace_bytes(N)
         ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         _lib.check(lib.frodo_track_pose(
