@@ -69,6 +69,10 @@ SIGNATURES = {
                                      [c_int, c_int, c_void_p, c_float, c_float, c_float] +
                                      [c_int] * 5 + [c_float, c_void_p, c_void_p, c_void_p,
                                                     c_size_t, c_void_p]),
+    "frodo_gn_pack_slot": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "frodo_gn_arena_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "frodo_gauss_newton_arena": (c_int, [ctypes.POINTER(GnParams)] + [c_void_p] * 13 + [c_int] * 6 +
+                                 [c_float, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "frodo_track_workspace_bytes": (c_size_t, [c_int]),
     "frodo_track_pose": (c_int, [ctypes.POINTER(TrackParams)] + [c_void_p] * 10 + [c_int] +
                          [c_void_p] * 5 + [c_size_t, c_void_p]),

@@ -384,6 +384,63 @@ int frodo_gauss_newton_rays_odom(const frodo_gn_params* params, float* Twc, cons
                 max_iter, delta_thresh, dx, info, workspace, workspace_bytes, &od, stream);
 }
 
+/* ---- device-resident keyframe / edge arena -------------------------------- */
+int frodo_gn_pack_slot(const float* X, const float* C, int K_arena, int slot, int N, float* XC,
+                       frodo_stream_t stream) {
+  FRODO_ARG_CHECK(K_arena >= 1 && slot >= 0 && slot < K_arena && N >= 0);
+  FRODO_ARG_CHECK(N == 0 || (X && C && XC));
+  FRODO_ARG_CHECK((reinterpret_cast<uintptr_t>(XC) & 15) == 0);
+  return launch_gn_pack_slot(X, C, K_arena, slot, N, XC, static_cast<cudaStream_t>(stream));
+}
+
+size_t frodo_gn_arena_workspace_bytes(int K_arena, int E, int N) {
+  GnWorkspace ws;
+  gn_carve_workspace(nullptr, K_arena, E, N, &ws);
+  return ws.packed_off;  // everything but the packed pointmaps, which the arena owns
+}
+
+int frodo_gauss_newton_arena(const frodo_gn_params* params, float* Twc, const float* Xs,
+                             const float* Cs, const float* Kmat, const float* XC_packed,
+                             const int32_t* ii_slot, const int32_t* jj_slot,
+                             const int32_t* ii_rank, const int32_t* jj_rank,
+                             const int32_t* pose_slot, const int64_t* idx_ii2jj,
+                             const uint8_t* valid_match, const float* Q, int K_arena, int K_solve,
+                             int N, int E, int num_fix, int max_iter, float delta_thresh,
+                             float* dx, int32_t* info, void* workspace, size_t workspace_bytes,
+                             frodo_stream_t stream) {
+  FRODO_ARG_CHECK(params != nullptr && K_arena >= 1 && K_solve >= 1 && K_solve <= K_arena);
+  FRODO_ARG_CHECK(N >= 0 && E >= 0 && E <= 65535 && num_fix >= 0 && num_fix <= K_solve);
+  FRODO_ARG_CHECK(params->mode != FRODO_GN_CALIB || Kmat != nullptr);
+  FRODO_ARG_CHECK(workspace != nullptr &&
+                  workspace_bytes >= frodo_gn_arena_workspace_bytes(K_arena, E, N));
+  FRODO_ARG_CHECK(Twc && pose_slot && (K_solve == num_fix || dx));
+  FRODO_ARG_CHECK(E == 0 || (Xs && Cs && ii_slot && jj_slot && ii_rank && jj_rank && idx_ii2jj &&
+                             valid_match && Q));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  GnWorkspace ws;
+  gn_carve_workspace(workspace, K_arena, E, N, &ws);
+  FRODO_CUDA_TRY(cudaMemsetAsync(ws.scalars, 0, 8 * sizeof(int32_t), s));
+  FRODO_CUDA_TRY(cudaMemsetAsync(ws.tickets, 0, (size_t)(E > 0 ? E : 1) * sizeof(int32_t), s));
+  int32_t* done = ws.scalars + 1;
+  int32_t* winfo = ws.scalars + 2;
+  const float* XC = (N % 16) == 0 ? XC_packed : nullptr;
+  for (int it = 0; it < max_iter; ++it) {
+    // data rows = arena slots; system rows = ranks among the participating keyframes
+    int rc = launch_gn_accumulate(*params, Twc, Xs, Cs, Kmat, XC, ii_slot, jj_slot, idx_ii2jj,
+                                  valid_match, Q, K_arena, N, E, ws.partials, ws.tickets,
+                                  ws.edge_blocks, done, s);
+    if (rc) return rc;
+    rc = launch_gn_assemble(ws.edge_blocks, ii_rank, jj_rank, E, K_solve, num_fix, ws.Hg, done, s);
+    if (rc) return rc;
+    rc = launch_gn_solve_retract(ws.Hg, Twc, dx, K_solve, num_fix, delta_thresh, done, winfo,
+                                 ws.chol, s, pose_slot);
+    if (rc) return rc;
+  }
+  if (info != nullptr)
+    FRODO_CUDA_TRY(cudaMemcpyAsync(info, winfo, 2 * sizeof(int32_t), cudaMemcpyDeviceToDevice, s));
+  return FRODO_OK;
+}
+
 size_t frodo_track_workspace_bytes(int N) { return track_workspace_bytes(N); }
 
 int frodo_track_pose(const frodo_track_params* params, const float* Xf, const int64_t* idx_f2k,

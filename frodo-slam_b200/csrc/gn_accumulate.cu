@@ -938,6 +938,20 @@ int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float*
   return FRODO_OK;
 }
 
+int launch_gn_pack_slot(const float* X, const float* C, int K_total, int slot, int N, float* XC,
+                        cudaStream_t s) {
+  if (N == 0) return FRODO_OK;
+  const int NB = (N + kTilePts - 1) / kTilePts;
+  const size_t slots = (size_t)NB * kRaysThreads;
+  const int blocks = (int)((slots + 255) / 256);
+  float4* xc = reinterpret_cast<float4*>(XC);
+  float4* xc_row = xc + (size_t)slot * N;
+  float4* xp_row = xc + (size_t)K_total * N + (size_t)slot * NB * kRaysThreads * 2;
+  pack_points_kernel<<<blocks, 256, 0, s>>>(X, C, xc_row, xp_row, 1, N, NB);
+  FRODO_CUDA_TRY(cudaGetLastError());
+  return FRODO_OK;
+}
+
 int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const float* Xs,
                          const float* Cs, const float* Kmat, const float* XC,
                          const int32_t* ii_row, const int32_t* jj_row, const int64_t* idx,

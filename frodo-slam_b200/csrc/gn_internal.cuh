@@ -48,6 +48,9 @@ int launch_gn_add_odom(const GnOdom& od, const float* Twc, int K, int num_fix, d
 size_t gn_packed_bytes(int K, int N);
 int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float* XC,
                           cudaStream_t s);
+// One keyframe (X [N,3], C [N]) into row `slot` of a packed region laid out for K_total keyframes.
+int launch_gn_pack_slot(const float* X, const float* C, int K_total, int slot, int N, float* XC,
+                        cudaStream_t s);
 // XC: pointmaps packed by launch_gn_pack_points (XC [K][N] float4, then XP), or NULL.
 int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const float* Xs,
                          const float* Cs, const float* Kmat, const float* XC,
@@ -59,10 +62,10 @@ int launch_gn_assemble(const double* edge_blocks, const int32_t* ii_row, const i
                        int E, int K, int num_fix, double* Hg, const int32_t* done, cudaStream_t s);
 int launch_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fix,
                             float delta_thresh, int32_t* done, int32_t* info, double* chol_scratch,
-                            cudaStream_t s);
+                            cudaStream_t s, const int32_t* pose_rows = nullptr);
 size_t gn_chol_scratch_bytes(int n);
 int launch_chol_cluster(double* Hg, float* Twc, float* dx, int K, int num_fix, float delta_thresh,
                         int32_t* done, int32_t* info, double* chol_scratch, int* handled,
-                        cudaStream_t s);
+                        cudaStream_t s, const int32_t* pose_rows = nullptr);
 
 }  // namespace frodo

@@ -95,10 +95,13 @@ __device__ inline void retract_pose(float* P, const float* xi) {
 
 // dx = -x (fp32, :977, :191-192), ||dx||_2 < delta_thresh (:986-989), pose
 // retraction (pose_retr_kernel :522-560).  Called by all THREADS threads of one CTA.
+// pose_rows (may be NULL): row of Twc that holds keyframe r of the linear system's ordering
+// (keyframe arena, graph.py); NULL = identity, the reference's dense [K,8] layout.
 template <int THREADS>
 __device__ inline void finish_update(const double* x, float* __restrict__ Twc, float* __restrict__ dx,
                               int n, int nopt, int num_fix, float delta_thresh,
-                              int32_t* __restrict__ done, int32_t* __restrict__ info) {
+                              int32_t* __restrict__ done, int32_t* __restrict__ info,
+                              const int32_t* __restrict__ pose_rows = nullptr) {
   __shared__ float nrm_part[THREADS / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   float local = 0.0f;
@@ -116,11 +119,12 @@ __device__ inline void finish_update(const double* x, float* __restrict__ Twc, f
 #pragma unroll
     for (int c = 0; c < 7; ++c) xi[c] = dx[k * 7 + c];
     float P[8];
+    const size_t row = pose_rows ? (size_t)pose_rows[k + num_fix] : (size_t)(k + num_fix);
 #pragma unroll
-    for (int c = 0; c < 8; ++c) P[c] = Twc[(size_t)(k + num_fix) * 8 + c];
+    for (int c = 0; c < 8; ++c) P[c] = Twc[row * 8 + c];
     retract_pose(P, xi);
 #pragma unroll
-    for (int c = 0; c < 8; ++c) Twc[(size_t)(k + num_fix) * 8 + c] = P[c];
+    for (int c = 0; c < 8; ++c) Twc[row * 8 + c] = P[c];
   }
   if (tid == 0) {
     float tot = 0.0f;

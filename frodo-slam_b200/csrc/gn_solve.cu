@@ -34,7 +34,7 @@ using namespace pose_update;
 __global__ void __launch_bounds__(kSolveThreads)
 solve_retract_kernel(double* __restrict__ A, float* __restrict__ Twc, float* __restrict__ dx,
                      int n, int K, int num_fix, float delta_thresh, int32_t* __restrict__ done,
-                     int32_t* __restrict__ info) {
+                     int32_t* __restrict__ info, const int32_t* __restrict__ pose_rows) {
   if (done != nullptr && *done != 0) return;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   SolveSmem& sm = *reinterpret_cast<SolveSmem*>(smem_raw);
@@ -199,7 +199,7 @@ solve_retract_kernel(double* __restrict__ A, float* __restrict__ Twc, float* __r
     __syncthreads();
   }
 
-  finish_update<kSolveThreads>(y, Twc, dx, n, nopt, num_fix, delta_thresh, done, info);
+  finish_update<kSolveThreads>(y, Twc, dx, n, nopt, num_fix, delta_thresh, done, info, pose_rows);
 }
 
 
@@ -207,13 +207,13 @@ solve_retract_kernel(double* __restrict__ A, float* __restrict__ Twc, float* __r
 
 int launch_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fix,
                             float delta_thresh, int32_t* done, int32_t* info, double* chol_scratch,
-                            cudaStream_t s) {
+                            cudaStream_t s, const int32_t* pose_rows) {
   const int n = 7 * (K - num_fix);
   if (n <= 0) return FRODO_OK;
   // fast path: cluster-resident tiled Cholesky (gn_chol_cluster.cu)
   int handled = 0;
   const int rc = launch_chol_cluster(Hg, Twc, dx, K, num_fix, delta_thresh, done, info,
-                                     chol_scratch, &handled, s);
+                                     chol_scratch, &handled, s, pose_rows);
   if (rc != FRODO_OK || handled) return rc;
   // fallback for systems that do not fit the cluster's shared memory
   static bool attr_set = false;
@@ -224,7 +224,8 @@ int launch_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fi
     attr_set = true;
   }
   solve_retract_kernel<<<1, kSolveThreads, sizeof(SolveSmem), s>>>(Hg, Twc, dx, n, K, num_fix,
-                                                                  delta_thresh, done, info);
+                                                                  delta_thresh, done, info,
+                                                                  pose_rows);
   FRODO_CUDA_TRY(cudaGetLastError());
   return FRODO_OK;
 }

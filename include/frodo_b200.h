@@ -20,6 +20,7 @@
  *   mast3r_slam/backend/src/gn.cpp:29-62     gauss_newton_rays_odom
  *   mast3r_slam/matching.py:8-110            match() and its helpers (Python in the reference)
  *   mast3r_slam/tracker.py:397-517           the tracker's pose solve (Python in the reference)
+ *   mast3r_slam/global_opt.py:186-224        per-solve graph packing (Python in the reference)
  */
 #ifndef FRODO_B200_H
 #define FRODO_B200_H
@@ -224,6 +225,37 @@ int frodo_gauss_newton_rays_odom(const frodo_gn_params* params, float* Twc, cons
                                  int K, int N, int E, int num_fix, int max_iter,
                                  float delta_thresh, float* dx, int32_t* info, void* workspace,
                                  size_t workspace_bytes, frodo_stream_t stream);
+
+/* ---- device-resident keyframe / edge arena --------------------------------
+ * The reference re-stacks every keyframe's pointmap from CPU shared memory and every edge tensor
+ * on each solve (FactorGraph.get_poses_points / prep_two_way_edges, global_opt.py:186-224;
+ * SharedKeyframes, frame.py:374-390).  Here keyframes and directed edges live in caller-owned
+ * device arrays with fixed capacity (host side: frodo-slam_b200/graph.py); a keyframe is packed
+ * once when it is written, and a solve addresses the arena through three small index arrays.
+ *
+ * frodo_gn_pack_slot: X [N,3], C [N] of ONE keyframe -> row `slot` of a packed region of
+ *   frodo_gn_packed_bytes(K_arena, N) bytes (same layout as frodo_gn_pack_points for K_arena).
+ * frodo_gauss_newton_arena: the loop of frodo_gauss_newton over arena rows.
+ *   Twc [K_arena,8], Xs [K_arena,N,3], Cs [K_arena,N], XC_packed (may be NULL): the arena;
+ *   ii_slot, jj_slot [E] i32: arena rows of every directed edge's keyframes (data addressing);
+ *   ii_rank, jj_rank [E] i32: their rank among the sorted unique keyframe ids of the edges
+ *     (get_unique_kf_idx, global_opt.py:180-184): rows of the linear system, the first num_fix
+ *     ranks are fixed;  pose_slot [K_solve] i32: rank -> arena row (where dx is applied);
+ *   idx_ii2jj [E,N] i64, valid_match [E,N] u8, Q [E,N] f32: the edge arena (first E rows).
+ *   dx [K_solve - num_fix, 7], info as frodo_gauss_newton.
+ *   workspace: frodo_gn_arena_workspace_bytes(K_arena, E, N). */
+int frodo_gn_pack_slot(const float* X, const float* C, int K_arena, int slot, int N, float* XC,
+                       frodo_stream_t stream);
+size_t frodo_gn_arena_workspace_bytes(int K_arena, int E, int N);
+int frodo_gauss_newton_arena(const frodo_gn_params* params, float* Twc, const float* Xs,
+                             const float* Cs, const float* Kmat, const float* XC_packed,
+                             const int32_t* ii_slot, const int32_t* jj_slot,
+                             const int32_t* ii_rank, const int32_t* jj_rank,
+                             const int32_t* pose_slot, const int64_t* idx_ii2jj,
+                             const uint8_t* valid_match, const float* Q, int K_arena, int K_solve,
+                             int N, int E, int num_fix, int max_iter, float delta_thresh,
+                             float* dx, int32_t* info, void* workspace, size_t workspace_bytes,
+                             frodo_stream_t stream);
 
 /* ---- the tracker's frame-to-keyframe pose solve -----------------------
  * FrameTracker.opt_pose_ray_dist_sim3 / opt_pose_calib_sim3 / solve, mast3r_slam/tracker.py:397-517
