@@ -35,6 +35,14 @@ class TrackParams(ctypes.Structure):
                 ("height", c_int), ("width", c_int), ("pixel_border", c_int), ("z_eps", c_float)]
 
 
+class OdomTerms(ctypes.Structure):
+    """struct frodo_gn_odom_terms (include/frodo_b200.h)."""
+    _fields_ = [("odom_ii_row", c_void_p), ("odom_jj_row", c_void_p), ("odom_rank", c_void_p),
+                ("Tij", c_void_p), ("tij_stride", c_int), ("E_odom", c_int), ("s_bar", c_void_p),
+                ("sigma_odom_t", c_float), ("sigma_odom_r", c_float),
+                ("sigma_scale_prior", c_float), ("blocks", c_void_p), ("blocks_bytes", c_size_t)]
+
+
 # name -> (restype, argtypes); kept in sync with include/frodo_b200.h (tests check this)
 SIGNATURES = {
     "frodo_version": (c_int, []),
@@ -72,7 +80,11 @@ SIGNATURES = {
     "frodo_gn_pack_slot": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "frodo_gn_arena_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "frodo_gauss_newton_arena": (c_int, [ctypes.POINTER(GnParams)] + [c_void_p] * 13 + [c_int] * 6 +
-                                 [c_float, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+                                 [c_float, ctypes.POINTER(OdomTerms), c_void_p, c_void_p, c_void_p,
+                                  c_size_t, c_void_p]),
+    "frodo_gn_odom_blocks_bytes": (c_size_t, [c_int]),
+    "frodo_gn_add_odom": (c_int, [ctypes.POINTER(OdomTerms), c_void_p, c_void_p, c_int, c_int,
+                                  c_void_p, c_void_p, c_void_p]),
     "frodo_track_workspace_bytes": (c_size_t, [c_int]),
     "frodo_track_pose": (c_int, [ctypes.POINTER(TrackParams)] + [c_void_p] * 10 + [c_int] +
                          [c_void_p] * 5 + [c_size_t, c_void_p]),

@@ -384,6 +384,43 @@ int frodo_gauss_newton_rays_odom(const frodo_gn_params* params, float* Twc, cons
                 max_iter, delta_thresh, dx, info, workspace, workspace_bytes, &od, stream);
 }
 
+size_t frodo_gn_odom_blocks_bytes(int E_odom) { return gn_odom_blocks_bytes(E_odom); }
+
+static GnOdom odom_from_terms(const frodo_gn_odom_terms* t) {
+  GnOdom od;
+  od.odom_ii = t->odom_ii_row;
+  od.odom_jj = t->odom_jj_row;
+  od.Tij = t->Tij;
+  od.stride = t->tij_stride;
+  od.Eo = t->E_odom;
+  od.s_bar = t->s_bar;
+  od.sigma_t = t->sigma_odom_t;
+  od.sigma_r = t->sigma_odom_r;
+  od.sigma_scale = t->sigma_scale_prior;
+  return od;
+}
+
+static int check_odom_terms(const frodo_gn_odom_terms* t) {
+  FRODO_ARG_CHECK(t != nullptr && t->E_odom >= 0);
+  FRODO_ARG_CHECK(t->E_odom == 0 || (t->odom_ii_row && t->odom_jj_row && t->odom_rank && t->Tij &&
+                                     t->tij_stride >= 7));
+  FRODO_ARG_CHECK(t->blocks != nullptr && t->blocks_bytes >= gn_odom_blocks_bytes(t->E_odom));
+  return FRODO_OK;
+}
+
+int frodo_gn_add_odom(const frodo_gn_odom_terms* terms, const float* Twc,
+                      const int32_t* pose_rows, int K, int num_fix, double* Hg,
+                      const int32_t* done, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(K >= 1 && num_fix >= 0 && num_fix <= K);
+  FRODO_ARG_CHECK(K == num_fix || (Twc && Hg));
+  int rc = check_odom_terms(terms);
+  if (rc) return rc;
+  const GnOdom od = odom_from_terms(terms);
+  return launch_gn_add_odom_rows(od, Twc, K, num_fix, Hg, done, terms->odom_rank,
+                                 static_cast<double*>(terms->blocks), pose_rows,
+                                 static_cast<cudaStream_t>(stream));
+}
+
 /* ---- device-resident keyframe / edge arena -------------------------------- */
 int frodo_gn_pack_slot(const float* X, const float* C, int K_arena, int slot, int N, float* XC,
                        frodo_stream_t stream) {
@@ -406,9 +443,14 @@ int frodo_gauss_newton_arena(const frodo_gn_params* params, float* Twc, const fl
                              const int32_t* pose_slot, const int64_t* idx_ii2jj,
                              const uint8_t* valid_match, const float* Q, int K_arena, int K_solve,
                              int N, int E, int num_fix, int max_iter, float delta_thresh,
-                             float* dx, int32_t* info, void* workspace, size_t workspace_bytes,
-                             frodo_stream_t stream) {
+                             const frodo_gn_odom_terms* odom, float* dx, int32_t* info,
+                             void* workspace, size_t workspace_bytes, frodo_stream_t stream) {
   FRODO_ARG_CHECK(params != nullptr && K_arena >= 1 && K_solve >= 1 && K_solve <= K_arena);
+  if (odom != nullptr) {
+    FRODO_ARG_CHECK(params->mode == FRODO_GN_RAYS);
+    const int orc = check_odom_terms(odom);
+    if (orc) return orc;
+  }
   FRODO_ARG_CHECK(N >= 0 && E >= 0 && E <= 65535 && num_fix >= 0 && num_fix <= K_solve);
   FRODO_ARG_CHECK(params->mode != FRODO_GN_CALIB || Kmat != nullptr);
   FRODO_ARG_CHECK(workspace != nullptr &&
@@ -432,6 +474,12 @@ int frodo_gauss_newton_arena(const frodo_gn_params* params, float* Twc, const fl
     if (rc) return rc;
     rc = launch_gn_assemble(ws.edge_blocks, ii_rank, jj_rank, E, K_solve, num_fix, ws.Hg, done, s);
     if (rc) return rc;
+    if (odom != nullptr) {
+      const GnOdom od = odom_from_terms(odom);
+      rc = launch_gn_add_odom_rows(od, Twc, K_solve, num_fix, ws.Hg, done, odom->odom_rank,
+                                   static_cast<double*>(odom->blocks), pose_slot, s);
+      if (rc) return rc;
+    }
     rc = launch_gn_solve_retract(ws.Hg, Twc, dx, K_solve, num_fix, delta_thresh, done, winfo,
                                  ws.chol, s, pose_slot);
     if (rc) return rc;

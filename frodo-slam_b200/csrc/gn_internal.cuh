@@ -42,6 +42,10 @@ struct GnOdom {
   float sigma_t, sigma_r, sigma_scale;
 };
 size_t gn_odom_scratch_bytes(int Eo);
+size_t gn_odom_blocks_bytes(int Eo);
+int launch_gn_add_odom_rows(const GnOdom& od, const float* Twc, int K, int num_fix, double* Hg,
+                            const int32_t* done, const int32_t* rows, double* blocks,
+                            const int32_t* pose_rows, cudaStream_t s);
 int launch_gn_add_odom(const GnOdom& od, const float* Twc, int K, int num_fix, double* Hg,
                        const int32_t* done, void* scratch, cudaStream_t s);
 // Bytes of the packed pointmap region (XC [K][N] float4 + XP padded to 512-point blocks).

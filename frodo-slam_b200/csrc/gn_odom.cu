@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(64)
 odom_add_kernel(const double* __restrict__ blocks, const int32_t* __restrict__ rows, int Eo,
                 const float* __restrict__ Twc, const double* __restrict__ s_bar,
                 float sigma_scale, int nblk, int num_fix, double* __restrict__ Hg,
-                const int32_t* __restrict__ done) {
+                const int32_t* __restrict__ done, const int32_t* __restrict__ pose_rows) {
   if (done != nullptr && *done != 0) return;
   const int bid = blockIdx.x;
   int a = (int)((sqrtf(8.0f * (float)bid + 1.0f) - 1.0f) * 0.5f);
@@ -228,7 +228,8 @@ odom_add_kernel(const double* __restrict__ blocks, const int32_t* __restrict__ r
   if (a == b && s_bar != nullptr && (double)sigma_scale > 1e-9 && (tid == 48 || tid == 55)) {
     const int row = a + num_fix;
     const double sbar = s_bar[row];
-    const double si = (double)Twc[8 * row + 6];  // sic: column 6 (q_w), see the header comment
+    const size_t trow = pose_rows ? (size_t)pose_rows[row] : (size_t)row;  // arena: rank -> slot
+    const double si = (double)Twc[8 * trow + 6];  // sic: column 6 (q_w), see the header comment
     if (sbar > 1e-6 && si > 1e-6) {
       const double info = 1.0 / ((double)sigma_scale * (double)sigma_scale);
       acc += tid == 48 ? info : info * log(si / sbar);
@@ -252,12 +253,25 @@ size_t gn_odom_scratch_bytes(int Eo) {
 
 int launch_gn_add_odom(const GnOdom& od, const float* Twc, int K, int num_fix, double* Hg,
                        const int32_t* done, void* scratch, cudaStream_t s) {
+  const int32_t* rows = static_cast<const int32_t*>(scratch);
+  const size_t rows_bytes =
+      (2 * (size_t)(od.Eo > 0 ? od.Eo : 1) * sizeof(int32_t) + 255) / 256 * 256;
+  double* blocks = reinterpret_cast<double*>(static_cast<char*>(scratch) + rows_bytes);
+  return launch_gn_add_odom_rows(od, Twc, K, num_fix, Hg, done, rows, blocks, nullptr, s);
+}
+
+size_t gn_odom_blocks_bytes(int Eo) {
+  return (size_t)(Eo > 0 ? Eo : 1) * kOdomBlock * sizeof(double);
+}
+
+// rows [2 Eo]: system ranks of the odometry endpoints (ii ranks, then jj ranks); od.odom_ii/jj
+// index the rows of Twc; pose_rows (may be NULL): system rank -> row of Twc for the scale prior.
+int launch_gn_add_odom_rows(const GnOdom& od, const float* Twc, int K, int num_fix, double* Hg,
+                            const int32_t* done, const int32_t* rows, double* blocks,
+                            const int32_t* pose_rows, cudaStream_t s) {
   const int nblk = K - num_fix;
   if (nblk <= 0) return FRODO_OK;
   const int Eo = od.Eo > 0 ? od.Eo : 0;
-  const int32_t* rows = static_cast<const int32_t*>(scratch);
-  const size_t rows_bytes = (2 * (size_t)(Eo > 0 ? Eo : 1) * sizeof(int32_t) + 255) / 256 * 256;
-  double* blocks = reinterpret_cast<double*>(static_cast<char*>(scratch) + rows_bytes);
   if (Eo > 0) {
     odom_blocks_kernel<<<(Eo + 63) / 64, 64, 0, s>>>(Twc, od.Tij, od.stride, od.odom_ii,
                                                       od.odom_jj, Eo, od.sigma_t, od.sigma_r,
@@ -266,7 +280,7 @@ int launch_gn_add_odom(const GnOdom& od, const float* Twc, int K, int num_fix, d
   }
   const int nb = nblk * (nblk + 1) / 2;
   odom_add_kernel<<<nb, 64, 0, s>>>(blocks, rows, Eo, Twc, od.s_bar, od.sigma_scale, nblk,
-                                    num_fix, Hg, done);
+                                    num_fix, Hg, done, pose_rows);
   FRODO_CUDA_TRY(cudaGetLastError());
   return FRODO_OK;
 }

@@ -11,6 +11,7 @@ import torch
 import torch.distributed as dist
 
 from . import _lib
+from ._lib import OdomTerms
 from .backends import _gn_validate, _ptr, _stream
 
 
@@ -49,6 +50,8 @@ class ShardedGaussNewton:
             jj_row = torch.empty(E, dtype=torch.int32, device=dev)
             _lib.check(lib.frodo_gn_edge_index(_ptr(ii), _ptr(jj), E, _ptr(ii_row), _ptr(jj_row),
                                                None, _stream()))
+            self._ids = torch.unique(torch.cat([ii, jj]), sorted=True)  # for set_odometry
+            self.odom = None
             self.ii_row = ii_row[lo:hi].contiguous()
             self.jj_row = jj_row[lo:hi].contiguous()
             # packed fast path: pointmaps repacked inside the workspace, once per solve
@@ -56,6 +59,36 @@ class ShardedGaussNewton:
             if self.N % 16 == 0 and self.E_local > 0:
                 off = lib.frodo_gn_workspace_packed_offset(self.num_kf, max(self.E_local, 1), self.N)
                 self.xc = ctypes.c_void_p(self.ws.data_ptr() + off)
+
+    def set_odometry(self, odom_ii, odom_jj, Tij, s_bar, sigma_odom_t, sigma_odom_r,
+                     sigma_scale_prior):
+        """The extra terms of gauss_newton_rays_odom (gn_kernels.cu:1792-1934): every rank adds
+        them to the summed system after the all-reduce (replicated: O(K) work, identical bits on
+        every rank).  Same conventions as the single-GPU op: ids index Twc rows directly and
+        are ranked against the visual keyframe list (:1121-1122, :1829)."""
+        dev = self.Twc.device
+        Eo = int(odom_ii.shape[0])
+        rank = torch.cat([torch.searchsorted(self._ids, odom_ii.to(dev)),
+                          torch.searchsorted(self._ids, odom_jj.to(dev))]).to(torch.int32)
+        sb = None
+        if s_bar is not None:
+            sb = torch.as_tensor(s_bar).to(device=dev, dtype=torch.float64).contiguous()
+        nb = self.lib.frodo_gn_odom_blocks_bytes(Eo)
+        blocks = torch.empty(nb, dtype=torch.uint8, device=dev)
+        oi, oj = odom_ii.to(dev).contiguous(), odom_jj.to(dev).contiguous()
+        Tij = Tij.to(dev).contiguous()
+        t = OdomTerms()
+        t.odom_ii_row = oi.data_ptr() if Eo else None
+        t.odom_jj_row = oj.data_ptr() if Eo else None
+        t.odom_rank = rank.data_ptr() if Eo else None
+        t.Tij = Tij.data_ptr() if Eo else None
+        t.tij_stride = int(Tij.shape[1]) if Eo else 0
+        t.E_odom = Eo
+        t.s_bar = sb.data_ptr() if sb is not None else None
+        t.sigma_odom_t, t.sigma_odom_r = float(sigma_odom_t), float(sigma_odom_r)
+        t.sigma_scale_prior = float(sigma_scale_prior)
+        t.blocks, t.blocks_bytes = blocks.data_ptr(), nb
+        self.odom = (t, (oi, oj, rank, Tij, sb, blocks))
 
     def solve(self, max_iter, delta_thresh):
         lib, dev = self.lib, self.Twc.device
@@ -77,6 +110,10 @@ class ShardedGaussNewton:
                     self.num_fix, _ptr(self.Hg), None, done, _ptr(self.ws), self.nbytes, st))
                 if dist.is_initialized() and dist.get_world_size(self.group) > 1:
                     dist.all_reduce(self.Hg, op=dist.ReduceOp.SUM, group=self.group)
+                if self.odom is not None:
+                    _lib.check(lib.frodo_gn_add_odom(ctypes.byref(self.odom[0]), _ptr(self.Twc),
+                                                     None, self.num_kf, self.num_fix,
+                                                     _ptr(self.Hg), done, st))
                 _lib.check(lib.frodo_gn_solve_retract(
                     _ptr(self.Hg), _ptr(self.Twc), _ptr(self.dx), self.num_kf, self.num_fix,
                     float(delta_thresh), done, info, _ptr(self.ws), self.nbytes, st))

@@ -23,11 +23,13 @@ from the host-side id lists -- the reference also keeps the ids in Python lists 
 ``frodo_gauss_newton_arena``: no pointmap or edge tensor is touched by the host again.
 No CPU fallback: tensors must live on the arena's CUDA device.
 """
+import bisect
 import ctypes
 
 import torch
 
 from . import _lib
+from ._lib import OdomTerms
 from .backends import make_params
 
 __all__ = ["KeyframeGraphArena"]
@@ -206,7 +208,50 @@ class KeyframeGraphArena:
         E = len(ii2)
         return uniq, t[0:E], t[E:2 * E], t[2 * E:3 * E], t[3 * E:4 * E], t[4 * E:], E
 
-    def solve(self, mode, num_fix, max_iter, delta_thresh, K=None, **params):
+    def _odom_terms(self, uniq, odom):
+        """frodo_gn_odom_terms for `odom` = dict(odom_ii, odom_jj: keyframe ids (lists or
+        tensors), Tij [Eo,7|8] f32 device, s_bar [Ku] by rank of the unique keyframes or None,
+        sigma_odom_t, sigma_odom_r, sigma_scale_prior).  Rows of Twc = arena slots; system
+        ranks = searchsorted in the visual keyframe list (gn_kernels.cu:1829)."""
+        oi = [int(x) for x in (odom["odom_ii"].tolist() if torch.is_tensor(odom["odom_ii"])
+                               else odom["odom_ii"])]
+        oj = [int(x) for x in (odom["odom_jj"].tolist() if torch.is_tensor(odom["odom_jj"])
+                               else odom["odom_jj"])]
+        Eo = len(oi)
+        if len(oj) != Eo:
+            raise ValueError("odom_ii and odom_jj must have the same length")
+        rows = torch.tensor([self.slot_of(k) for k in oi] + [self.slot_of(k) for k in oj],
+                            dtype=torch.int64).to(self.dev, non_blocking=True)
+        rank = torch.tensor([bisect.bisect_left(uniq, k) for k in oi] +
+                            [bisect.bisect_left(uniq, k) for k in oj],
+                            dtype=torch.int32).to(self.dev, non_blocking=True)
+        Tij = odom["Tij"]
+        if Eo > 0 and (not Tij.is_cuda or Tij.dtype != torch.float32 or Tij.dim() != 2 or
+                       Tij.shape[0] != Eo or Tij.shape[1] < 7 or not Tij.is_contiguous()):
+            raise RuntimeError("Tij must be a contiguous float32 [num_odom_edges, 7 or 8] device tensor")
+        sb = odom.get("s_bar")
+        if sb is not None:
+            sb = torch.as_tensor(sb).to(device=self.dev, dtype=torch.float64).contiguous()
+            if sb.numel() != len(uniq):
+                raise RuntimeError("s_bar must hold one scale target per participating keyframe")
+        nb = self.lib.frodo_gn_odom_blocks_bytes(Eo)
+        blocks = torch.empty(nb, dtype=torch.uint8, device=self.dev)
+        t = OdomTerms()
+        t.odom_ii_row = rows[:Eo].data_ptr() if Eo else None
+        t.odom_jj_row = rows[Eo:].data_ptr() if Eo else None
+        t.odom_rank = rank.data_ptr() if Eo else None
+        t.Tij = Tij.data_ptr() if Eo else None
+        t.tij_stride = int(Tij.shape[1]) if Eo else 0
+        t.E_odom = Eo
+        t.s_bar = sb.data_ptr() if sb is not None else None
+        t.sigma_odom_t = float(odom["sigma_odom_t"])
+        t.sigma_odom_r = float(odom["sigma_odom_r"])
+        t.sigma_scale_prior = float(odom["sigma_scale_prior"])
+        t.blocks = blocks.data_ptr()
+        t.blocks_bytes = nb
+        return t, (rows, rank, sb, blocks, Tij)  # keep the tensors alive through the launch
+
+    def solve(self, mode, num_fix, max_iter, delta_thresh, K=None, odom=None, **params):
         """One global optimisation over the edges currently in the arena, poses updated in
         place.  mode / params as ``backends.make_params`` ("rays": sigma_ray, sigma_dist,
         C_thresh, Q_thresh; "points": sigma_point, ...; "calib": + height, width,
@@ -221,10 +266,13 @@ class KeyframeGraphArena:
             if K is None or not K.is_cuda or K.dtype != torch.float32 or K.numel() != 9:
                 raise RuntimeError("calib needs K [3,3] float32 on the device")
             K = K.contiguous()
+        if odom is not None and mode != "rays":
+            raise ValueError("odometry terms exist for the rays residual only")
         with torch.cuda.device(self.dev):
             dx = torch.zeros((max(Ku - num_fix, 0), 7), dtype=torch.float32, device=self.dev)
             if max_iter <= 0 or Ku - num_fix <= 0:
                 return dx, uniq
+            terms, keep = self._odom_terms(uniq, odom) if odom is not None else (None, None)
             nbytes = self.lib.frodo_gn_arena_workspace_bytes(self.Kcap, E, self.N)
             if self._ws is None or self._ws_bytes < nbytes:
                 self._ws = torch.empty(nbytes, dtype=torch.uint8, device=self.dev)
@@ -233,10 +281,24 @@ class KeyframeGraphArena:
                 ctypes.byref(prm), _ptr(self.Twc), _ptr(self.Xs), _ptr(self.Cs), _ptr(K),
                 _ptr(self.packed), _ptr(ii_slot), _ptr(jj_slot), _ptr(ii_rank), _ptr(jj_rank),
                 _ptr(pose_slot), _ptr(self.idx), _ptr(self.valid), _ptr(self.Q), self.Kcap, Ku,
-                self.N, E, int(num_fix), int(max_iter), float(delta_thresh), _ptr(dx), None,
+                self.N, E, int(num_fix), int(max_iter), float(delta_thresh),
+                ctypes.byref(terms) if terms is not None else None, _ptr(dx), None,
                 _ptr(self._ws), self._ws_bytes,
                 ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+            del keep
         return dx, uniq
+
+    def solve_rays_odom(self, odom_ii, odom_jj, Tij, s_bar, sigma_odom_t, sigma_odom_r, sigma_ray,
+                        sigma_dist, sigma_scale_prior, C_thresh, Q_thresh, num_fix, max_iter,
+                        delta_thresh):
+        """The arena form of ``gauss_newton_rays_odom`` (gn.cpp:29-45; the op the fork's
+        ``solve_GN_rays`` calls, global_opt.py:260): same scalar arguments in the same order;
+        odom_ii / odom_jj are keyframe ids, s_bar [number of participating keyframes]."""
+        odom = dict(odom_ii=odom_ii, odom_jj=odom_jj, Tij=Tij, s_bar=s_bar,
+                    sigma_odom_t=sigma_odom_t, sigma_odom_r=sigma_odom_r,
+                    sigma_scale_prior=sigma_scale_prior)
+        return self.solve("rays", num_fix, max_iter, delta_thresh, odom=odom, sigma_ray=sigma_ray,
+                          sigma_dist=sigma_dist, C_thresh=C_thresh, Q_thresh=Q_thresh)
 
     def solve_rays(self, sigma_ray, sigma_dist, C_thresh, Q_thresh, num_fix, max_iter,
                    delta_thresh):

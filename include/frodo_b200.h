@@ -226,6 +226,30 @@ int frodo_gauss_newton_rays_odom(const frodo_gn_params* params, float* Twc, cons
                                  float delta_thresh, float* dx, int32_t* info, void* workspace,
                                  size_t workspace_bytes, frodo_stream_t stream);
 
+/* The odometry / scale-prior terms of gauss_newton_rays_odom as a separate step, for drivers
+ * that own the iteration loop (the edge-sharded multi-GPU driver adds them after its all-reduce;
+ * the arena driver below takes them as an argument).  Adds the blocks of
+ * odom_constraint_kernel_left_perturb_log and apply_scale_prior_cpu (gn_kernels.cu:1106-1286,
+ * :1716-1790) to Hg [(n+1) x n], n = 7 (K - num_fix), in odometry-edge order. */
+typedef struct frodo_gn_odom_terms {
+  const int64_t* odom_ii_row; /* [E_odom] rows of Twc holding the two poses of each edge        */
+  const int64_t* odom_jj_row;
+  const int32_t* odom_rank;   /* [2 E_odom] rows of the linear system + num_fix (searchsorted of
+                                 the ids in the visual keyframe list, :1829): ii ranks, jj ranks */
+  const float* Tij;           /* [E_odom, tij_stride] measured relative poses                    */
+  int tij_stride;
+  int E_odom;
+  const double* s_bar;        /* [K] device, by system rank; NULL disables the scale prior       */
+  float sigma_odom_t, sigma_odom_r, sigma_scale_prior;
+  void* blocks;               /* scratch, frodo_gn_odom_blocks_bytes(E_odom) bytes               */
+  size_t blocks_bytes;
+} frodo_gn_odom_terms;
+size_t frodo_gn_odom_blocks_bytes(int E_odom);
+/* pose_rows (may be NULL): system rank -> row of Twc (arena); NULL = identity. */
+int frodo_gn_add_odom(const frodo_gn_odom_terms* terms, const float* Twc,
+                      const int32_t* pose_rows, int K, int num_fix, double* Hg,
+                      const int32_t* done, frodo_stream_t stream);
+
 /* ---- device-resident keyframe / edge arena --------------------------------
  * The reference re-stacks every keyframe's pointmap from CPU shared memory and every edge tensor
  * on each solve (FactorGraph.get_poses_points / prep_two_way_edges, global_opt.py:186-224;
@@ -242,6 +266,7 @@ int frodo_gauss_newton_rays_odom(const frodo_gn_params* params, float* Twc, cons
  *     (get_unique_kf_idx, global_opt.py:180-184): rows of the linear system, the first num_fix
  *     ranks are fixed;  pose_slot [K_solve] i32: rank -> arena row (where dx is applied);
  *   idx_ii2jj [E,N] i64, valid_match [E,N] u8, Q [E,N] f32: the edge arena (first E rows).
+ *   odom (may be NULL; rays only): the gauss_newton_rays_odom terms, rows = arena rows.
  *   dx [K_solve - num_fix, 7], info as frodo_gauss_newton.
  *   workspace: frodo_gn_arena_workspace_bytes(K_arena, E, N). */
 int frodo_gn_pack_slot(const float* X, const float* C, int K_arena, int slot, int N, float* XC,
@@ -254,8 +279,8 @@ int frodo_gauss_newton_arena(const frodo_gn_params* params, float* Twc, const fl
                              const int32_t* pose_slot, const int64_t* idx_ii2jj,
                              const uint8_t* valid_match, const float* Q, int K_arena, int K_solve,
                              int N, int E, int num_fix, int max_iter, float delta_thresh,
-                             float* dx, int32_t* info, void* workspace, size_t workspace_bytes,
-                             frodo_stream_t stream);
+                             const frodo_gn_odom_terms* odom, float* dx, int32_t* info,
+                             void* workspace, size_t workspace_bytes, frodo_stream_t stream);
 
 /* ---- the tracker's frame-to-keyframe pose solve -----------------------
  * FrameTracker.opt_pose_ray_dist_sim3 / opt_pose_calib_sim3 / solve, mast3r_slam/tracker.py:397-517

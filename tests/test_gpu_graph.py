@@ -189,3 +189,62 @@ def test_remove_keyframe_and_reinsert(dev):
     B, _, _ = _build(dev, "window8", 48, 64, id_base=0, Kcap=8, Ecap=12)
     B.solve_rays(GP["sigma_ray"], GP["sigma_dist"], GP["C_conf"], GP["Q_conf"], 1, 3, 0.0)
     assert (A.poses(uniq) - B.poses(uniq)).abs().max().item() < 1e-5
+
+
+# ---------------------------------------------- gauss_newton_rays_odom through the arena / dist
+
+OP = synth.ODOM_PARAMS
+
+
+@pytest.mark.parametrize("id_base,Kcap", [(0, 8), (10, 12)])
+@pytest.mark.parametrize("num_fix", [1, 2])
+def test_arena_rays_odom_equals_dropin_bitwise(dev, id_base, Kcap, num_fix):
+    import mast3r_slam_backends as be
+    A, g, und = _build(dev, "window8", 48, 64, id_base=id_base, Kcap=Kcap, Ecap=12)
+    od = synth.odometry_edges(g, device=dev)
+    uniq, Twc, Xs, Cs, ii, jj, idx, valid, Q = A.stacked_inputs()
+    # the drop-in uses ids as rows of the stacked Twc (gn_kernels.cu:1121-1122): hand it ranks
+    base = torch.tensor(uniq, device=dev)
+    ii_r, jj_r = torch.searchsorted(base, ii), torch.searchsorted(base, jj)
+    Twc_ref = Twc.clone()
+    dx_ref = be.gauss_newton_rays_odom(
+        Twc_ref, Xs, Cs, ii_r, jj_r, idx, valid, Q, od["odom_ii"], od["odom_jj"], od["Tij"],
+        od["s_bar"], OP["sigma_odom_t"], OP["sigma_odom_r"], OP["sigma_ray"], GP["sigma_dist"],
+        OP["sigma_scale_prior"], GP["C_conf"], GP["Q_conf"], num_fix, 3, 0.0)[0]
+    dx, uniq2 = A.solve_rays_odom(od["odom_ii"] + id_base, od["odom_jj"] + id_base, od["Tij"],
+                                  od["s_bar"], OP["sigma_odom_t"], OP["sigma_odom_r"],
+                                  OP["sigma_ray"], GP["sigma_dist"], OP["sigma_scale_prior"],
+                                  GP["C_conf"], GP["Q_conf"], num_fix, 3, 0.0)
+    assert uniq2 == uniq
+    assert torch.equal(dx, dx_ref) and torch.equal(A.poses(uniq), Twc_ref)
+    # and the odometry terms do change the result
+    B, _, _ = _build(dev, "window8", 48, 64, id_base=id_base, Kcap=Kcap, Ecap=12)
+    B.solve_rays(OP["sigma_ray"], GP["sigma_dist"], GP["C_conf"], GP["Q_conf"], num_fix, 3, 0.0)
+    assert (B.poses(uniq) - A.poses(uniq)).abs().max().item() > 1e-6
+
+
+def test_sharded_driver_with_odometry_equals_single_call_bitwise(dev):
+    """dist.ShardedGaussNewton.set_odometry (terms added after the all-reduce) at world 1."""
+    import mast3r_slam_backends as be
+    from frodo_slam_b200 import backends, dist as fdist
+    K, und = synth.graph_edges("window8")
+    g = synth.keyframe_graph(K, 48, 64, und, seed=3, device="cpu")
+    g = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in g.items()}
+    od = synth.odometry_edges(g, device=dev)
+    E, N = g["ii"].shape[0], 48 * 64
+    Ta = g["Twc"].clone()
+    da = be.gauss_newton_rays_odom(
+        Ta, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"], g["valid_match"], g["Q"],
+        od["odom_ii"], od["odom_jj"], od["Tij"], od["s_bar"], OP["sigma_odom_t"],
+        OP["sigma_odom_r"], OP["sigma_ray"], GP["sigma_dist"], OP["sigma_scale_prior"],
+        GP["C_conf"], GP["Q_conf"], 1, 3, 0.0)[0]
+    prm = backends.make_params("rays", sigma_ray=OP["sigma_ray"], sigma_dist=GP["sigma_dist"],
+                               C_thresh=GP["C_conf"], Q_thresh=GP["Q_conf"])
+    Tb = g["Twc"].clone()
+    sg = fdist.ShardedGaussNewton(prm, Tb, g["Xs"], g["Cs"], None, g["ii"], g["jj"],
+                                  g["idx_ii2jj"].view(E, N), g["valid_match"].view(E, N),
+                                  g["Q"].view(E, N), 0, E, 1)
+    sg.set_odometry(od["odom_ii"], od["odom_jj"], od["Tij"], od["s_bar"], OP["sigma_odom_t"],
+                    OP["sigma_odom_r"], OP["sigma_scale_prior"])
+    db = sg.solve(3, 0.0)
+    assert torch.equal(da, db) and torch.equal(Ta, Tb)
