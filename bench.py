@@ -16,6 +16,8 @@ D2H of the poses inside the timed region.
 For N > 1 launch with torchrun (one rank per GPU).  See the task contract in DESIGN.md.
 """
 import argparse
+import contextlib
+import io
 import json
 import os
 import subprocess
@@ -682,10 +684,26 @@ def main():
     ap.add_argument("--no-matching", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
-    if args.impl == "reference":
-        main_reference(args)
-    else:
-        main_ours(args)
+    # stdout carries exactly ONE line, the JSON: anything libraries write to fd 1 meanwhile
+    # (NCCL's version banner, the reference's solver log) is routed to stderr.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    out = io.StringIO()
+    with contextlib.redirect_stdout(out):
+        if args.impl == "reference":
+            main_reference(args)
+        else:
+            main_ours(args)
+    sys.stdout.flush()
+    lines = [ln for ln in out.getvalue().splitlines() if ln.strip()]
+    json_lines = [ln for ln in lines if ln.lstrip().startswith("{")]
+    for ln in lines:
+        if ln not in json_lines:
+            print(ln, file=sys.stderr)
+    if json_lines:
+        os.write(real_stdout, (json_lines[-1] + "\n").encode())
+    os.close(real_stdout)
 
 
 if __name__ == "__main__":
