@@ -176,14 +176,16 @@ def gn_params():
                                 C_thresh=gp["C_conf"], Q_thresh=gp["Q_conf"]), gp
 
 
-def run_matching(device, B, steps, warmup, peak, be=None):
-    """px-matches/s of iter_proj + refine_matches over B pairs at 512x384 (inputs in HBM).
-    `be`: the backend module (default: this repo's drop-in; the reference arm passes the
+def run_matching(device, B, steps, warmup, peak, be=None, hw=None):
+    """px-matches/s of iter_proj + refine_matches over B pairs at 512x384 (or `hw`), inputs in
+    HBM.  `be`: the backend module (default: this repo's drop-in; the reference arm passes the
     reference's own pybind module)."""
     if be is None:
         import mast3r_slam_backends as be
     from frodo_slam_b200 import synth
     mp = synth.MATCH_PARAMS
+    H_IMG, W_IMG = hw if hw is not None else (globals()["H_IMG"], globals()["W_IMG"])
+    N_PTS = H_IMG * W_IMG
     base = 8  # distinct synthetic pairs, tiled to B (inputs stay > L2: 38 MB/pair)
     d = synth.matching_pairs(min(base, B), H_IMG, W_IMG, seed=0, device=device)
     rep = (B + base - 1) // base
@@ -210,7 +212,7 @@ def run_matching(device, B, steps, warmup, peak, be=None):
     val = px / (ms * 1e-3)
     return {
         "metric": "px-matches/s (iter_proj+refine_matches)", "value": val, "unit": "px/s",
-        "pairs": B, "resolution": "512x384", "ms_per_step": ms / steps,
+        "pairs": B, "resolution": f"{W_IMG}x{H_IMG}", "ms_per_step": ms / steps,
         "iter_proj": {"px_per_s": px / (ms_ip * 1e-3),
                       "roofline_frac": 65 * px / (ms_ip * 1e-3) / 1e9 / peak},
         "refine_matches": {"px_per_s": px / (ms_rm * 1e-3),
@@ -306,6 +308,34 @@ def cpu_baseline_gn(g_np, seconds=12.0):
     return {"value": 1.0 / t_iter, "unit": "iters/s", "cores": cores, "kind": "port",
             "sample": f"{ns} of {E} edges x {N_PTS} points, {passes} passes, accumulation only "
                       f"(solve excluded), extrapolated x{E / ns:.0f}"}
+
+
+def run_tracking(dev):
+    """The tracker's frame-to-keyframe pose solve (tracker.py:397-517) on one
+    512x384 frame through frodo_slam_b200.tracking (one persistent cooperative kernel): time per
+    solve with the reference's stopping rule, and per iteration from fixed 1- and 50-iteration
+    runs.  profiles/bench_track.py adds the PyTorch formulation of the same loop."""
+    from frodo_slam_b200 import synth, tracking
+    c = synth.tracking_case(H_IMG, W_IMG, seed=7, pose_noise=0.01)
+    t = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in c.items()}
+    tp = dict(synth.TRACK_PARAMS)
+    fixed = dict(tp, rel_error=0.0, delta_norm=0.0)
+
+    def call(cfg):
+        return tracking.track_pose("rays", t["Xf_all"], t["Xk"], t["T_WCf"], t["T_WCk"], t["Qk"],
+                                   t["valid"], idx_f2k=t["idx_f2k"], cfg=cfg)
+
+    iters = int(call(tp)["info"][0].item())
+    n = 50
+    us = 1e3 * timed_steps(lambda: call(tp), n, 5) / n
+    us1 = 1e3 * timed_steps(lambda: call(dict(fixed, max_iters=1)), n, 3) / n
+    us50 = 1e3 * timed_steps(lambda: call(fixed), n, 3) / n
+    return {"metric": "tracker pose solves/s (opt_pose_ray_dist_sim3), 512x384 frame",
+            "value": 1e6 / us, "unit": "solves/s", "us_per_solve": us, "iterations": iters,
+            "us_per_iteration": (us50 - us1) / 49.0, "points": N_PTS,
+            "prologue_bytes": N_PTS * 37, "gpu_launches_per_solve": 1,
+            "note": "after a one-off 37 B/point prologue the points stay in shared memory; "
+                    "per-iteration global traffic is 36 doubles per CTA"}
 
 
 def run_arena_e2e(dev, g, Twc0, idx, valid, Q, gp, iters, steps):
@@ -551,8 +581,15 @@ def main_ours(args):
         if world == 1:
             torch.cuda.empty_cache()
             matching["match_call"] = run_match_pipeline(dev, min(Bm, 64), 3, 2, peak)
+            torch.cuda.empty_cache()
+            # the other resolution of BASELINE.json configs[4] (batched tracking sweep)
+            m224 = run_matching(dev, Bm, 3, 2, peak, hw=(224, 224))
+            matching["sweep_224x224"] = {k: m224[k] for k in ("value", "unit", "pairs", "resolution",
+                                                              "ms_per_step", "iter_proj",
+                                                              "refine_matches")}
     if g_np is not None:
         cpu = cpu_baseline_gn(g_np)
+    tracking = run_tracking(dev) if (world == 1 and not args.no_matching) else None
 
     if rank == 0:
         line = {
@@ -568,6 +605,7 @@ def main_ours(args):
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
             "gpu_launches": args.steps * (1 + 3 * iters),  # pack + (accumulate, assemble, solve)/iter
             "matching": matching,
+            "tracking": tracking,
         }
         print(json.dumps(line))
     if world > 1:

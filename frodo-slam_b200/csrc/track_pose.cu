@@ -31,7 +31,8 @@ constexpr int kTrkThreads = 512;
 constexpr int kTrkWarps = kTrkThreads / 32;
 constexpr int kRec = 8;        // floats per point record
 constexpr int kSums = 36;      // 28 (upper triangle of H) + 7 (v) + 1 (cost)
-constexpr int kGroups = 7;     // partial-summation groups (7 * 36 = 252 threads)
+constexpr int kGroups = 14;    // partial-summation groups (14 * 36 = 504 threads)
+constexpr int kSumUnroll = 12; // partials per thread and pass, all loads issued before the adds
 constexpr int kMaxSmemPts = 6400;  // 6400 * 32 B = 200 KB of records per CTA
 
 struct TrackArgs {
@@ -248,39 +249,61 @@ __global__ void __launch_bounds__(kTrkThreads, 1) track_pose_kernel(const TrackA
   const int cap = a.cap;
 
   // ---- prologue: gather the frame's points, form the iteration-invariant records ---------
-  for (int p = tid; p < cnt; p += kTrkThreads) {
-    const int n = start + p;
-    const long long m = a.idx ? a.idx[n] : (long long)n;
-    float r[kRec];
-    bool ok = a.valid[n] != 0;
-    r[0] = a.Xf[m * 3 + 0]; r[1] = a.Xf[m * 3 + 1]; r[2] = a.Xf[m * 3 + 2];
-    const float q = a.Qk[n];
-    if (MODE == FRODO_GN_RAYS) {
-      const float k0 = a.Xk[(size_t)n * 3 + 0], k1 = a.Xk[(size_t)n * 3 + 1],
-                  k2 = a.Xk[(size_t)n * 3 + 2];
-      const float d = sqrtf(k0 * k0 + k1 * k1 + k2 * k2);
-      const float d_inv = 1.0f / d;
-      r[3] = d_inv * k0; r[4] = d_inv * k1; r[5] = d_inv * k2; r[6] = d;
-      r[7] = ok ? sqrtf(q) : 0.0f;
-    } else {
-      ok = ok && a.valid_meas[n] != 0;
-      r[3] = a.meas[(size_t)n * 3 + 0]; r[4] = a.meas[(size_t)n * 3 + 1];
-      r[5] = a.meas[(size_t)n * 3 + 2];
-      r[6] = ok ? sqrtf(q) : 0.0f;
-      r[7] = 0.0f;
-    }
-    if (!ok) {  // zero information: keep the arithmetic finite whatever the inputs hold
-      r[0] = 0.f; r[1] = 0.f; r[2] = 1.f; r[3] = 0.f; r[4] = 0.f;
-      r[5] = MODE == FRODO_GN_RAYS ? 1.f : 0.f;
-      r[6] = MODE == FRODO_GN_RAYS ? 1.f : 0.f;
-      r[7] = 0.f;
-    }
-    if (p < cap) {
+  // Four points per thread and pass: all streamed loads (idx, valid, Q, Xk | meas) are issued
+  // first, then the four data-dependent gathers of Xf, then the arithmetic -- the prologue is
+  // latency-bound (<= 3 points per thread at 512x384), so loads in flight are what count.
+  constexpr int kPro = 4;
+  for (int p0 = tid; p0 < cnt; p0 += kPro * kTrkThreads) {
+    long long m[kPro];
+    float q[kPro], km[kPro][3], xf[kPro][3];
+    bool ok[kPro];
 #pragma unroll
-      for (int c = 0; c < kRec; ++c) rec_s[c * cap + p] = r[c];
-    } else {
+    for (int u = 0; u < kPro; ++u) {
+      const int p = p0 + u * kTrkThreads;
+      const int n = start + min(p, cnt - 1);  // clamped: loads stay unconditional
+      m[u] = a.idx ? a.idx[n] : (long long)n;
+      ok[u] = a.valid[n] != 0;
+      q[u] = a.Qk[n];
+      const float* src = (MODE == FRODO_GN_RAYS ? a.Xk : a.meas) + (size_t)n * 3;
+      km[u][0] = src[0]; km[u][1] = src[1]; km[u][2] = src[2];
+      if (MODE != FRODO_GN_RAYS) ok[u] = ok[u] && a.valid_meas[n] != 0;
+    }
 #pragma unroll
-      for (int c = 0; c < kRec; ++c) a.overflow[(size_t)c * a.N + n] = r[c];
+    for (int u = 0; u < kPro; ++u) {
+      const float* x = a.Xf + m[u] * 3;
+      xf[u][0] = x[0]; xf[u][1] = x[1]; xf[u][2] = x[2];
+    }
+#pragma unroll
+    for (int u = 0; u < kPro; ++u) {
+      const int p = p0 + u * kTrkThreads;
+      if (p >= cnt) break;
+      const int n = start + p;
+      float r[kRec];
+      r[0] = xf[u][0]; r[1] = xf[u][1]; r[2] = xf[u][2];
+      if (MODE == FRODO_GN_RAYS) {
+        const float k0 = km[u][0], k1 = km[u][1], k2 = km[u][2];
+        const float d = sqrtf(k0 * k0 + k1 * k1 + k2 * k2);
+        const float d_inv = 1.0f / d;
+        r[3] = d_inv * k0; r[4] = d_inv * k1; r[5] = d_inv * k2; r[6] = d;
+        r[7] = ok[u] ? sqrtf(q[u]) : 0.0f;
+      } else {
+        r[3] = km[u][0]; r[4] = km[u][1]; r[5] = km[u][2];
+        r[6] = ok[u] ? sqrtf(q[u]) : 0.0f;
+        r[7] = 0.0f;
+      }
+      if (!ok[u]) {  // zero information: keep the arithmetic finite whatever the inputs hold
+        r[0] = 0.f; r[1] = 0.f; r[2] = 1.f; r[3] = 0.f; r[4] = 0.f;
+        r[5] = MODE == FRODO_GN_RAYS ? 1.f : 0.f;
+        r[6] = MODE == FRODO_GN_RAYS ? 1.f : 0.f;
+        r[7] = 0.f;
+      }
+      if (p < cap) {
+#pragma unroll
+        for (int c = 0; c < kRec; ++c) rec_s[c * cap + p] = r[c];
+      } else {
+#pragma unroll
+        for (int c = 0; c < kRec; ++c) a.overflow[(size_t)c * a.N + n] = r[c];
+      }
     }
   }
   if (tid == 0) {
@@ -365,7 +388,16 @@ __global__ void __launch_bounds__(kTrkThreads, 1) track_pose_kernel(const TrackA
     if (tid < kGroups * kSums) {
       const int grp = tid / kSums, l = tid - grp * kSums;
       double s = 0.0;
-      for (int c = grp; c < G; c += kGroups) s += __ldcg(part + (size_t)c * kSums + l);
+      for (int c0 = grp; c0 < G; c0 += kGroups * kSumUnroll) {
+        double vals[kSumUnroll];
+#pragma unroll
+        for (int u = 0; u < kSumUnroll; ++u) {
+          const int c = c0 + u * kGroups;
+          vals[u] = c < G ? __ldcg(part + (size_t)c * kSums + l) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < kSumUnroll; ++u) s += vals[u];
+      }
       grp_part[grp][l] = s;
     }
     __syncthreads();
