@@ -318,7 +318,7 @@ __device__ __forceinline__ void edge_epilogue(float (&S)[28], float (&v)[7], con
     for (int ch = 0; ch < nchunks; ++ch) acc += (double)__ldcg(p + (size_t)ch * kGnBlock);
     Sd[threadIdx.x] = acc;
   }
-  if (threadIdx.x == 64) adjoint_matrix(Ti, Md);
+  if (threadIdx.x == (THREADS > 64 ? 64 : THREADS - 1)) adjoint_matrix(Ti, Md);
   if (threadIdx.x == 0) tickets[e] = 0;  // ready for the next iteration
   epi_sync<THREADS, BAR>();
   if (threadIdx.x < 49) {
@@ -473,7 +473,7 @@ gn_accumulate_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
 #if FRODO_RAYS_WS
 #define FRODO_RAYS_THREADS 512
 #else
-#define FRODO_RAYS_THREADS 128   // 4 CTAs x 128 threads per SM: 475 us; 2 x 256: 485 us
+#define FRODO_RAYS_THREADS 128   // 4 CTAs x 128 threads per SM: 473 us; 2 x 256: 485 us; 8 x 64: 519 us
 #endif
 #endif
 constexpr int kRaysThreads = FRODO_RAYS_THREADS;        // threads per CTA of the rays kernel
