@@ -85,6 +85,8 @@ SIGNATURES = {
     "frodo_gn_odom_blocks_bytes": (c_size_t, [c_int]),
     "frodo_gn_add_odom": (c_int, [ctypes.POINTER(OdomTerms), c_void_p, c_void_p, c_int, c_int,
                                   c_void_p, c_void_p, c_void_p]),
+    "frodo_gn_peer_allreduce": (c_int, [c_void_p, c_void_p, c_size_t, c_int, c_int, c_int,
+                                        ctypes.c_uint32, c_void_p, c_size_t, c_void_p, c_void_p]),
     "frodo_track_workspace_bytes": (c_size_t, [c_int]),
     "frodo_track_pose": (c_int, [ctypes.POINTER(TrackParams)] + [c_void_p] * 10 + [c_int] +
                          [c_void_p] * 5 + [c_size_t, c_void_p]),

@@ -489,6 +489,18 @@ int frodo_gauss_newton_arena(const frodo_gn_params* params, float* Twc, const fl
   return FRODO_OK;
 }
 
+int frodo_gn_peer_allreduce(const void* peer_buffers, const void* peer_signal_pads,
+                            size_t buffer_offset_bytes, int signal_slot0, int rank, int world,
+                            uint32_t epoch, double* out, size_t n, const int32_t* done,
+                            frodo_stream_t stream) {
+  FRODO_ARG_CHECK(peer_buffers != nullptr && peer_signal_pads != nullptr && out != nullptr);
+  FRODO_ARG_CHECK(world >= 1 && world <= 16 && rank >= 0 && rank < world && signal_slot0 >= 0);
+  FRODO_ARG_CHECK((buffer_offset_bytes & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0);
+  FRODO_ARG_CHECK(epoch != 0);
+  return launch_peer_allreduce(peer_buffers, peer_signal_pads, buffer_offset_bytes, signal_slot0,
+                               rank, world, epoch, out, n, done, static_cast<cudaStream_t>(stream));
+}
+
 size_t frodo_track_workspace_bytes(int N) { return track_workspace_bytes(N); }
 
 int frodo_track_pose(const frodo_track_params* params, const float* Xf, const int64_t* idx_f2k,

@@ -55,6 +55,10 @@ int launch_match_finish(const int64_t* p1, const void* scores, bool scores_f16,
                         int B, int N, int W, cudaStream_t s);
 
 
+int launch_peer_allreduce(const void* bufs_dev, const void* pads_dev, size_t buf_offset,
+                          int pad_slot0, int rank, int world, uint32_t epoch, double* out, size_t n,
+                          const int32_t* done, cudaStream_t s);
+
 size_t track_workspace_bytes(int N);
 int launch_track_pose(const frodo_track_params& prm, const float* Xf, const int64_t* idx,
                       const float* Xk, const float* Qk, const uint8_t* valid, const float* meas,

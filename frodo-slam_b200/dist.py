@@ -6,6 +6,7 @@ test runs of the host logic), and every rank runs the identical Cholesky solve a
 pose retraction -- bit-identical inputs give bit-identical poses, so no broadcast of
 dx is needed.  The reference has no multi-GPU path."""
 import ctypes
+import os
 
 import torch
 import torch.distributed as dist
@@ -13,6 +14,46 @@ import torch.distributed as dist
 from . import _lib
 from ._lib import OdomTerms
 from .backends import _gn_validate, _ptr, _stream
+
+
+# Peer-memory exchange state, shared by every ShardedGaussNewton of a process (one symmetric
+# allocation per (group, size); the epoch counter must advance identically on all ranks, which it
+# does because all ranks execute the same sequence of solves).
+_PEER_CACHE = {}
+
+
+def _peer_state(numel, dev, group):
+    """Symmetric (peer-mapped) double buffer for `numel` doubles + signal words, or None when
+    torch's symmetric memory cannot serve this group (then NCCL's all-reduce is used).
+    FRODO_PEER_REDUCE=0 forces NCCL."""
+    if os.environ.get("FRODO_PEER_REDUCE", "1") == "0" or dev.type != "cuda":
+        return None
+    key = (id(group), dev.index, numel)
+    if key in _PEER_CACHE:
+        return _PEER_CACHE[key]
+    st = None
+    try:
+        import torch.distributed._symmetric_memory as symm
+        pg = group if group is not None else dist.group.WORLD
+        world = dist.get_world_size(pg)
+        if world <= 16:
+            padded = (numel + 1) // 2 * 2
+            buf = symm.empty(2 * padded, dtype=torch.float64, device=dev)
+            buf.zero_()
+            hdl = symm.rendezvous(buf, pg)
+            words = int(hdl.signal_pad_size) // 4
+            st = dict(buf=buf, hdl=hdl, bufs_dev=int(hdl.buffer_ptrs_dev),
+                      pads_dev=int(hdl.signal_pad_ptrs_dev), stride=padded * 8,
+                      slot0=words - 64 if words >= 128 else 0, epoch=0,
+                      rank=dist.get_rank(pg), world=world)
+            torch.cuda.synchronize(dev)
+            dist.barrier(pg)
+    except Exception as exc:  # no peer mapping on this system / build: NCCL serves the exchange
+        st = None
+        if os.environ.get("FRODO_PEER_REDUCE_DEBUG"):
+            print(f"[frodo] peer all-reduce unavailable, using NCCL: {exc!r}", flush=True)
+    _PEER_CACHE[key] = st
+    return st
 
 
 def edge_slice(num_edges, rank, world):
@@ -51,6 +92,11 @@ class ShardedGaussNewton:
             _lib.check(lib.frodo_gn_edge_index(_ptr(ii), _ptr(jj), E, _ptr(ii_row), _ptr(jj_row),
                                                None, _stream()))
             self._ids = torch.unique(torch.cat([ii, jj]), sorted=True)  # for set_odometry
+            # the exchange step: one kernel over NVLink peer memory (csrc/peer_reduce.cu) when
+            # torch can map the ranks' buffers into each other, NCCL's all-reduce otherwise
+            self.peer = None
+            if dist.is_initialized() and dist.get_world_size(group) > 1 and n > 0:
+                self.peer = _peer_state((n + 1) * n, dev, group)
             self.odom = None
             self.ii_row = ii_row[lo:hi].contiguous()
             self.jj_row = jj_row[lo:hi].contiguous()
@@ -102,13 +148,27 @@ class ShardedGaussNewton:
             if self.xc is not None and max_iter > 0:
                 _lib.check(lib.frodo_gn_pack_points(_ptr(self.Xs), _ptr(self.Cs), self.num_kf,
                                                     self.N, self.xc, st))
+            pr = self.peer
+            multi = dist.is_initialized() and dist.get_world_size(self.group) > 1
             for _ in range(max_iter):
+                hg_local = _ptr(self.Hg)
+                if pr is not None:  # this rank's partial goes to the symmetric buffer of this epoch
+                    pr["epoch"] += 1
+                    off = (pr["epoch"] & 1) * pr["stride"]
+                    hg_local = ctypes.c_void_p(pr["buf"].data_ptr() + off)
                 _lib.check(lib.frodo_gn_accumulate(
                     ctypes.byref(self.params), _ptr(self.Twc), _ptr(self.Xs), _ptr(self.Cs),
                     _ptr(self.K), self.xc, _ptr(self.ii_row), _ptr(self.jj_row), _ptr(self.idx),
                     _ptr(self.valid), _ptr(self.Q), self.num_kf, self.N, self.E_local,
-                    self.num_fix, _ptr(self.Hg), None, done, _ptr(self.ws), self.nbytes, st))
-                if dist.is_initialized() and dist.get_world_size(self.group) > 1:
+                    self.num_fix, hg_local, None, done, _ptr(self.ws), self.nbytes, st))
+                if pr is not None:
+                    # never skipped (done = NULL): the epochs stay consecutive on every rank,
+                    # which the double-buffering argument of peer_reduce.cu relies on
+                    _lib.check(lib.frodo_gn_peer_allreduce(
+                        ctypes.c_void_p(pr["bufs_dev"]), ctypes.c_void_p(pr["pads_dev"]), off,
+                        pr["slot0"], pr["rank"], pr["world"], pr["epoch"] & 0xFFFFFFFF or 1,
+                        _ptr(self.Hg), (self.n + 1) * self.n, None, st))
+                elif multi:
                     dist.all_reduce(self.Hg, op=dist.ReduceOp.SUM, group=self.group)
                 if self.odom is not None:
                     _lib.check(lib.frodo_gn_add_odom(ctypes.byref(self.odom[0]), _ptr(self.Twc),

@@ -250,6 +250,25 @@ int frodo_gn_add_odom(const frodo_gn_odom_terms* terms, const float* Twc,
                       const int32_t* pose_rows, int K, int num_fix, double* Hg,
                       const int32_t* done, frodo_stream_t stream);
 
+/* ---- the multi-GPU exchange step over NVLink peer memory ------------------------
+ * Sum of the per-rank systems [H | g] (n doubles each) in ONE kernel: cross-rank barrier on
+ * signal words + fixed-order (rank 0..world-1) sum with loads from the peers' memory, so every
+ * rank gets bit-identical totals.  The reference has no multi-GPU path; the NCCL all-reduce this
+ * replaces remains the fallback when no peer mapping is available.
+ *   peer_buffers: DEVICE array of `world` pointers to the ranks' symmetric buffers (same layout on
+ *     every rank; e.g. torch symmetric memory `buffer_ptrs_dev`); the partial system of this call
+ *     starts buffer_offset_bytes into each of them.  Callers alternate between two offsets
+ *     (double buffering by call parity): then this call's barrier is the only one needed.
+ *   peer_signal_pads: DEVICE array of `world` pointers to uint32 signal words (zero-initialised
+ *     once); words [signal_slot0, signal_slot0 + world) are used.
+ *   epoch: strictly increasing (by one) per call, identical on all ranks, never 0.
+ *   out [n] f64: local result.  `done` (may be NULL): when non-zero the call is skipped (it must
+ *     hold the same value on all ranks: it does, the poses are bit-identical). */
+int frodo_gn_peer_allreduce(const void* peer_buffers, const void* peer_signal_pads,
+                            size_t buffer_offset_bytes, int signal_slot0, int rank, int world,
+                            uint32_t epoch, double* out, size_t n, const int32_t* done,
+                            frodo_stream_t stream);
+
 /* ---- device-resident keyframe / edge arena --------------------------------
  * The reference re-stacks every keyframe's pointmap from CPU shared memory and every edge tensor
  * on each solve (FactorGraph.get_poses_points / prep_two_way_edges, global_opt.py:186-224;
