@@ -501,6 +501,21 @@ int frodo_gn_peer_allreduce(const void* peer_buffers, const void* peer_signal_pa
                                rank, world, epoch, out, n, done, static_cast<cudaStream_t>(stream));
 }
 
+int frodo_match_quality(const float* Q_src, const float* Q_dst, const float* C_src,
+                        const float* C_dst, const int64_t* idx, const uint8_t* valid_match,
+                        float Q_conf, float C_conf, float* Q_out, uint8_t* valid_opt,
+                        uint8_t* valid_q, int32_t* counts, int B, int N, int N_src,
+                        frodo_stream_t stream) {
+  FRODO_ARG_CHECK(B >= 0 && B <= 65535 && N >= 0 && N_src >= 0);
+  FRODO_ARG_CHECK(B == 0 || counts != nullptr);
+  FRODO_ARG_CHECK(B == 0 || N == 0 ||
+                  (Q_src && Q_dst && idx && valid_match && Q_out && valid_opt && valid_q &&
+                   N_src > 0));
+  return launch_match_quality(Q_src, Q_dst, C_src, C_dst, idx, valid_match, Q_conf, C_conf, Q_out,
+                              valid_opt, valid_q, counts, B, N, N_src,
+                              static_cast<cudaStream_t>(stream));
+}
+
 size_t frodo_track_workspace_bytes(int N) { return track_workspace_bytes(N); }
 
 int frodo_track_pose(const frodo_track_params* params, const float* Xf, const int64_t* idx_f2k,

@@ -55,6 +55,12 @@ int launch_match_finish(const int64_t* p1, const void* scores, bool scores_f16,
                         int B, int N, int W, cudaStream_t s);
 
 
+int launch_match_quality(const float* Q_src, const float* Q_dst, const float* C_src,
+                         const float* C_dst, const int64_t* idx, const uint8_t* valid_match,
+                         float Q_conf, float C_conf, float* Q_out, uint8_t* valid_opt,
+                         uint8_t* valid_q, int32_t* counts, int B, int N, int N_src,
+                         cudaStream_t s);
+
 int launch_peer_allreduce(const void* bufs_dev, const void* pads_dev, size_t buf_offset,
                           int pad_slot0, int rank, int world, uint32_t epoch, double* out, size_t n,
                           const int32_t* done, cudaStream_t s);

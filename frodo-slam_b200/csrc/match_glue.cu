@@ -179,6 +179,73 @@ match_finish_kernel(const longlong2* __restrict__ p1, const ScoreT* __restrict__
   }
 }
 
+// The per-edge quality glue the callers run after match(): tracker.py:194-206 and
+// FactorGraph.add_factors, global_opt.py:98-112 (six torch kernels + two boolean sums there).
+//   Q[n]         = sqrt(Q_src[b, idx[n]] * Q_dst[n])                    (fp32, one rounding each)
+//   valid_q[n]   = valid_match[n] & (Q[n] > Q_conf)
+//   valid_opt[n] = valid_q[n] & (C_src[b, idx[n]] > C_conf) & (C_dst[n] > C_conf)   (if C given)
+//   counts[b]    = (sum valid_opt, sum valid_q): numerators of match_frac
+// One thread per 4 consecutive points (16-byte streams); the two gathers are the only
+// data-dependent accesses.  Algorithmic bytes per point: idx 8 + Q 4+4 + valid 1 (+ C 4+4) in,
+// Q 4 + 2 masks out = 23 (31).
+constexpr int kQualThreads = 256;
+__global__ void __launch_bounds__(kQualThreads)
+match_quality_kernel(const float* __restrict__ Q_src, const float* __restrict__ Q_dst,
+                     const float* __restrict__ C_src, const float* __restrict__ C_dst,
+                     const int64_t* __restrict__ idx, const uint8_t* __restrict__ valid_match,
+                     float Q_conf, float C_conf, float* __restrict__ Q_out,
+                     uint8_t* __restrict__ valid_opt, uint8_t* __restrict__ valid_q,
+                     int32_t* __restrict__ counts, int N, int N_src) {
+  const int b = blockIdx.y;
+  const size_t row = (size_t)b * N;
+  const float* qs = Q_src + (size_t)b * N_src;
+  const float* cs = C_src ? C_src + (size_t)b * N_src : nullptr;
+  int n_opt = 0, n_q = 0;
+  const int stride = gridDim.x * kQualThreads * 4;
+  for (int n0 = (blockIdx.x * kQualThreads + threadIdx.x) * 4; n0 < N; n0 += stride) {
+    long long m[4];
+    float qd[4], cd[4], qg[4], cg[4];
+    bool vm[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int n = min(n0 + u, N - 1);  // clamped: loads stay unconditional
+      m[u] = idx[row + n];
+      qd[u] = Q_dst[row + n];
+      vm[u] = valid_match[row + n] != 0;
+      cd[u] = C_dst ? C_dst[row + n] : 0.0f;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      qg[u] = qs[m[u]];
+      cg[u] = cs ? cs[m[u]] : 0.0f;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int n = n0 + u;
+      if (n >= N) break;
+      const float q = __fsqrt_rn(__fmul_rn(qg[u], qd[u]));
+      const bool vq = vm[u] && (q > Q_conf);
+      bool vo = vq;
+      if (C_src) vo = vo && (cg[u] > C_conf);
+      if (C_dst) vo = vo && (cd[u] > C_conf);
+      Q_out[row + n] = q;
+      valid_q[row + n] = vq;
+      valid_opt[row + n] = vo;
+      n_q += vq;
+      n_opt += vo;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    n_opt += __shfl_xor_sync(0xffffffffu, n_opt, o);
+    n_q += __shfl_xor_sync(0xffffffffu, n_q, o);
+  }
+  if ((threadIdx.x & 31) == 0 && (n_opt | n_q)) {
+    atomicAdd(counts + 2 * b, n_opt);
+    atomicAdd(counts + 2 * b + 1, n_q);
+  }
+}
+
 int stream_blocks(size_t work_items) {
   const size_t want = (work_items + 255) / 256;
   const size_t cap = (size_t)kNumSMs * 8;  // 8 resident CTAs of 256 threads per SM
@@ -230,6 +297,25 @@ int launch_match_finish(const int64_t* p1, const void* scores, bool scores_f16,
     match_finish_kernel<float><<<stream_blocks(total), 256, 0, s>>>(
         reinterpret_cast<const longlong2*>(p1), static_cast<const float*>(scores), valid_in,
         threshold, idx, valid, W, total);
+  FRODO_CUDA_TRY(cudaGetLastError());
+  return FRODO_OK;
+}
+
+int launch_match_quality(const float* Q_src, const float* Q_dst, const float* C_src,
+                         const float* C_dst, const int64_t* idx, const uint8_t* valid_match,
+                         float Q_conf, float C_conf, float* Q_out, uint8_t* valid_opt,
+                         uint8_t* valid_q, int32_t* counts, int B, int N, int N_src,
+                         cudaStream_t s) {
+  if (B == 0) return FRODO_OK;
+  FRODO_CUDA_TRY(cudaMemsetAsync(counts, 0, (size_t)B * 2 * sizeof(int32_t), s));
+  if (N == 0) return FRODO_OK;
+  int bx = (N + kQualThreads * 4 - 1) / (kQualThreads * 4);
+  const int cap = (kNumSMs * 8 + B - 1) / B;
+  if (bx > cap) bx = cap;
+  if (bx < 1) bx = 1;
+  match_quality_kernel<<<dim3(bx, B), kQualThreads, 0, s>>>(Q_src, Q_dst, C_src, C_dst, idx,
+                                                            valid_match, Q_conf, C_conf, Q_out,
+                                                            valid_opt, valid_q, counts, N, N_src);
   FRODO_CUDA_TRY(cudaGetLastError());
   return FRODO_OK;
 }

@@ -24,7 +24,7 @@ from ._lib import MatchParams
 from .backends import _check, _check_contiguous, _ptr, _stream, iter_proj, refine_matches
 
 __all__ = ["match", "match_iterative_proj", "prep_for_iter_proj", "pixel_to_lin", "lin_to_pixel",
-           "DEFAULT_CFG"]
+           "match_quality", "DEFAULT_CFG"]
 
 # config/base.yaml:9-16
 DEFAULT_CFG = dict(max_iter=10, lambda_init=1e-8, convergence_thresh=1e-6, dist_thresh=1e-1,
@@ -140,3 +140,53 @@ def match(X11, X21, D11, D21, idx_1_to_2_init=None, cfg=None):
                                    _ptr(idx_1_to_2_init), _ptr(idx), _ptr(valid), b, h, w, F,
                                    ctypes.c_void_p(ws.data_ptr() + off), nbytes, _stream()))
     return idx, valid.unsqueeze(-1)
+
+
+def match_quality(Q_src, Q_dst, idx, valid_match, Q_conf, C_src=None, C_dst=None, C_conf=0.0):
+    """What the callers derive from a match before using it, in one kernel
+    (``frodo_match_quality``) instead of six torch kernels and two boolean sums:
+
+    * the tracker (tracker.py:194-206): ``Qk = sqrt(Qff[idx_f2k] * Qkf)``, ``valid_opt =
+      valid_match_k & (Cff[idx_f2k] > C_conf) & (Ckf > C_conf) & (Qk > Q_conf)``,
+      ``valid_kf = valid_match_k & (Qk > Q_conf)``, ``match_frac = valid_opt.sum() / numel``;
+    * ``FactorGraph.add_factors`` (global_opt.py:98-112): ``Qj = sqrt(Qii[b, idx_i2j] * Qji)``,
+      ``valid_j = valid_match_j & (Qj > Q_conf)``, ``match_frac_j`` (no confidence test: leave
+      ``C_src`` / ``C_dst`` unset).
+
+    Q_src, C_src ``[B,N_src(,1)]`` (or unbatched), Q_dst, C_dst, valid_match ``[B,N(,1)]``, idx
+    ``[B,N]`` int64.  Returns ``(Q, valid_opt, valid_q, counts)`` shaped like ``Q_dst`` /
+    ``valid_match``, ``counts [B,2] int32 = (sum valid_opt, sum valid_q)`` on the device
+    (``match_frac = counts[:, 0] / N``; nothing is read back here).  Bit-identical to torch."""
+    batched = idx.dim() >= 2
+    B = idx.shape[0] if batched else 1
+    N = idx.numel() // max(B, 1)
+    dev = idx.device
+    named = dict(Q_src=Q_src, Q_dst=Q_dst, idx=idx, valid_match=valid_match)
+    if C_src is not None:
+        named["C_src"] = C_src
+    if C_dst is not None:
+        named["C_dst"] = C_dst
+    _check_contiguous(**named)
+    _check(idx, "idx", torch.int64)
+    _check(valid_match, "valid_match", torch.bool, dev)
+    for name in ("Q_src", "Q_dst", "C_src", "C_dst"):
+        if name in named:
+            _check(named[name], name, torch.float32, dev)
+    N_src = Q_src.numel() // max(B, 1)
+    if Q_dst.numel() != B * N or valid_match.numel() != B * N or Q_src.numel() != B * N_src or \
+            (C_src is not None and C_src.numel() != B * N_src) or \
+            (C_dst is not None and C_dst.numel() != B * N):
+        raise RuntimeError("match_quality: Q_dst / C_dst / valid_match must be [B,N], Q_src / C_src "
+                           "[B,N_src]")
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        Q = torch.empty_like(Q_dst)
+        valid_opt = torch.empty_like(valid_match)
+        valid_q = torch.empty_like(valid_match)
+        counts = torch.empty((B, 2), dtype=torch.int32, device=dev)
+        _lib.check(lib.frodo_match_quality(
+            _ptr(Q_src), _ptr(Q_dst), _ptr(C_src), _ptr(C_dst), _ptr(idx), _ptr(valid_match),
+            float(Q_conf), float(C_conf), _ptr(Q), _ptr(valid_opt), _ptr(valid_q), _ptr(counts),
+            B, N, N_src, _stream()))
+    return Q, valid_opt, valid_q, counts
+

@@ -115,6 +115,20 @@ int frodo_match(const frodo_match_params* params, const float* X11, const float*
                 int64_t* idx_1_to_2, uint8_t* valid, int B, int H, int W, int F, void* workspace,
                 size_t workspace_bytes, frodo_stream_t stream);
 
+/* frodo_match_quality: what the callers compute from a match before using it -- the tracker
+ *   (mast3r_slam/tracker.py:194-206) and FactorGraph.add_factors (global_opt.py:98-112):
+ *     Q[b,n]         = sqrt(Q_src[b, idx[b,n]] * Q_dst[b,n])
+ *     valid_q[b,n]   = valid_match[b,n] & (Q[b,n] > Q_conf)                 (valid_kf / valid_j)
+ *     valid_opt[b,n] = valid_q & (C_src[b, idx[b,n]] > C_conf) & (C_dst[b,n] > C_conf)
+ *     counts[b]      = {sum valid_opt, sum valid_q}  (match_frac = counts / N), int32 [B,2]
+ *   Q_src, C_src [B,N_src] f32 (C_src / C_dst may be NULL: no confidence test), Q_dst, C_dst
+ *   [B,N] f32, idx [B,N] i64 in [0,N_src), valid_match [B,N] u8.  Bit-identical to torch. */
+int frodo_match_quality(const float* Q_src, const float* Q_dst, const float* C_src,
+                        const float* C_dst, const int64_t* idx, const uint8_t* valid_match,
+                        float Q_conf, float C_conf, float* Q_out, uint8_t* valid_opt,
+                        uint8_t* valid_q, int32_t* counts, int B, int N, int N_src,
+                        frodo_stream_t stream);
+
 /* ---- Gauss-Newton over the keyframe graph ---------------------------------
  * Shared tensor meanings (gn_kernels.cu:909-995):
  *   Twc [K,8] f32 = [t(3), q_xyzw(4), s], updated IN PLACE;  Xs [K,N,3] f32;

@@ -626,3 +626,27 @@ def track_meas_calib(Xf, Xk, K, img_size, depth_eps=1e-6):
     vmk = Xk2[:, 2:3] > depth_eps
     meas[~np.repeat(vmk, 3, axis=1)] = 0.0
     return Xf2, Xk2, meas, vmk
+
+
+def match_quality(Q_src, Q_dst, idx, valid_match, Q_conf, C_src=None, C_dst=None, C_conf=0.0):
+    """tracker.py:194-206 / global_opt.py:98-112 restated in numpy fp32 (batched [B,N]):
+    Q = sqrt(Q_src[b, idx] * Q_dst); valid_q = valid_match & (Q > Q_conf); valid_opt = valid_q &
+    (C_src[b, idx] > C_conf) & (C_dst > C_conf); counts = (sum valid_opt, sum valid_q) per b."""
+    idx = np.asarray(idx, np.int64)
+    B = idx.shape[0]
+    N = idx.reshape(B, -1).shape[1]
+    idx = idx.reshape(B, N)
+    qs = _f32(Q_src).reshape(B, -1)
+    qd = _f32(Q_dst).reshape(B, N)
+    vm = np.asarray(valid_match).reshape(B, N).astype(bool)
+    rows = np.arange(B)[:, None]
+    Q = np.sqrt((qs[rows, idx] * qd).astype(np.float32)).astype(np.float32)
+    vq = vm & (Q > np.float32(Q_conf))
+    vo = vq.copy()
+    if C_src is not None:
+        vo &= _f32(C_src).reshape(B, -1)[rows, idx] > np.float32(C_conf)
+    if C_dst is not None:
+        vo &= _f32(C_dst).reshape(B, N) > np.float32(C_conf)
+    counts = np.stack((vo.sum(axis=1), vq.sum(axis=1)), axis=1).astype(np.int32)
+    return Q, vo, vq, counts
+

@@ -171,3 +171,54 @@ def test_match_argument_errors(fm, dev):
         fm.match(a[0].double(), a[1], a[2], a[3])
     idx, valid = fm.match(a[0][:0], a[1][:0], a[2][:0], a[3][:0])   # empty batch
     assert idx.shape == (0, 16 * 32) and valid.shape == (0, 16 * 32, 1)
+
+
+# ------------------------------------------------ match_quality (tracker.py:194-206, global_opt.py:98-112)
+
+def _quality_inputs(B, N, N_src, seed):
+    g = torch.Generator().manual_seed(seed)
+    Qs = torch.rand(B, N_src, 1, generator=g) * 3.0
+    Qd = torch.rand(B, N, 1, generator=g) * 3.0
+    Cs = torch.rand(B, N_src, 1, generator=g) * 2.0 - 0.3
+    Cd = torch.rand(B, N, 1, generator=g) * 2.0 - 0.3
+    idx = torch.randint(0, N_src, (B, N), generator=g)
+    vm = torch.rand(B, N, 1, generator=g) < 0.8
+    return Qs, Qd, Cs, Cd, idx, vm
+
+
+@pytest.mark.parametrize("B,N,N_src", [(1, 48 * 64, 48 * 64), (3, 1001, 777), (2, 5, 9),
+                                       (1, 384 * 512, 384 * 512)])
+@pytest.mark.parametrize("with_conf", [True, False])
+def test_match_quality_bitwise_vs_torch_and_oracle(fm, dev, B, N, N_src, with_conf):
+    Qs, Qd, Cs, Cd, idx, vm = _quality_inputs(B, N, N_src, seed=B * 7 + N)
+    Q_conf, C_conf = 1.5, 0.25
+    # the reference's expressions (tracker.py:194-206), evaluated by torch ON THE GPU as the
+    # reference does (torch's CPU sqrt is not correctly rounded, CUDA's is)
+    rows = torch.arange(B, device=dev)[:, None]
+    Qs_d, Qd_d, Cs_d, Cd_d, idx_d, vm_d = (x.to(dev) for x in (Qs, Qd, Cs, Cd, idx, vm))
+    Q_t = torch.sqrt(Qs_d[rows, idx_d] * Qd_d)
+    vq_t = vm_d & (Q_t > Q_conf)
+    vo_t = vq_t & (Cs_d[rows, idx_d] > C_conf) & (Cd_d > C_conf) if with_conf else vq_t
+    Q_t, vq_t, vo_t = Q_t.cpu(), vq_t.cpu(), vo_t.cpu()
+    Q, vo, vq, counts = fm.match_quality(Qs.to(dev), Qd.to(dev), idx.to(dev), vm.to(dev), Q_conf,
+                                         Cs.to(dev) if with_conf else None,
+                                         Cd.to(dev) if with_conf else None, C_conf)
+    assert Q.shape == Qd.shape and vo.shape == vm.shape
+    assert torch.equal(Q.cpu(), Q_t) and torch.equal(vq.cpu(), vq_t) and torch.equal(vo.cpu(), vo_t)
+    assert counts.cpu().tolist() == [[int(vo_t[b].sum()), int(vq_t[b].sum())] for b in range(B)]
+    o = oracle.match_quality(Qs.numpy(), Qd.numpy(), idx.numpy(), vm.numpy(), Q_conf,
+                             Cs.numpy() if with_conf else None, Cd.numpy() if with_conf else None,
+                             C_conf)
+    assert np.array_equal(Q.cpu().numpy().reshape(B, N), o[0])
+    assert np.array_equal(vo.cpu().numpy().reshape(B, N), o[1])
+    assert np.array_equal(counts.cpu().numpy(), o[3])
+
+
+def test_match_quality_errors_and_empty(fm, dev):
+    Qs, Qd, Cs, Cd, idx, vm = _quality_inputs(2, 16, 16, seed=1)
+    with pytest.raises(RuntimeError):  # CPU tensors
+        fm.match_quality(Qs, Qd, idx, vm, 1.5)
+    with pytest.raises(RuntimeError):  # wrong size
+        fm.match_quality(Qs.to(dev), Qd.to(dev)[:, :8].contiguous(), idx.to(dev), vm.to(dev), 1.5)
+    e = fm.match_quality(Qs.to(dev)[:0], Qd.to(dev)[:0], idx.to(dev)[:0], vm.to(dev)[:0], 1.5)
+    assert e[0].numel() == 0 and e[3].shape == (0, 2)

@@ -135,3 +135,30 @@ def test_odometry_blocks_structure():
     gv = np.zeros(49)
     oracle.scale_prior(H, gv, g["Twc"].numpy(), od["s_bar"].numpy(), 1, 0.1)
     assert np.count_nonzero(H) == 6 and H[6, 6] == pytest.approx(100.0)  # keyframe 2 skipped
+
+
+def test_match_quality_oracle_equals_torch_expressions():
+    """tracker.py:194-206 / global_opt.py:98-112 evaluated by torch (CPU) vs the numpy restatement."""
+    import torch
+    from oracle import oracle
+    g = torch.Generator().manual_seed(3)
+    B, N, Ns = 3, 501, 377
+    Qs, Qd = torch.rand(B, Ns, 1, generator=g) * 3, torch.rand(B, N, 1, generator=g) * 3
+    Cs, Cd = torch.rand(B, Ns, 1, generator=g) - 0.3, torch.rand(B, N, 1, generator=g) - 0.3
+    idx = torch.randint(0, Ns, (B, N), generator=g)
+    vm = torch.rand(B, N, 1, generator=g) < 0.7
+    rows = torch.arange(B)[:, None]
+    Q = torch.sqrt(Qs[rows, idx] * Qd)
+    vq = vm & (Q > 1.5)
+    vo = vq & (Cs[rows, idx] > 0.1) & (Cd > 0.1)
+    o = oracle.match_quality(Qs.numpy(), Qd.numpy(), idx.numpy(), vm.numpy(), 1.5, Cs.numpy(),
+                             Cd.numpy(), 0.1)
+    # torch's CPU sqrt is a vectorised approximation (1 ulp off in ~0.6 % of the values); numpy's,
+    # like CUDA's sqrtf the reference runs on, is correctly rounded: compare to 1 ulp, and the
+    # masks away from the threshold
+    Qn = Q.numpy().reshape(B, N)
+    assert np.abs(o[0] - Qn).max() <= 2.4e-7 * 3
+    clear = np.abs(Qn - 1.5) > 1e-5
+    assert np.array_equal(o[1][clear], vo.numpy().reshape(B, N)[clear])
+    assert np.array_equal(o[2][clear], vq.numpy().reshape(B, N)[clear])
+    assert o[3].tolist() == [[int(o[1][b].sum()), int(o[2][b].sum())] for b in range(B)]
