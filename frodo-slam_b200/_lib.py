@@ -32,7 +32,8 @@ class TrackParams(ctypes.Structure):
     """struct frodo_track_params (include/frodo_b200.h)."""
     _fields_ = [("mode", c_int), ("sigma_a", c_float), ("sigma_b", c_float), ("huber", c_float),
                 ("max_iters", c_int), ("rel_error", c_float), ("delta_norm", c_float),
-                ("height", c_int), ("width", c_int), ("pixel_border", c_int), ("z_eps", c_float)]
+                ("height", c_int), ("width", c_int), ("pixel_border", c_int), ("z_eps", c_float),
+                ("raw_calib", c_int)]
 
 
 class OdomTerms(ctypes.Structure):

@@ -533,8 +533,10 @@ int frodo_track_pose(const frodo_track_params* params, const float* Xf, const in
   if (params->mode == FRODO_GN_RAYS) {
     FRODO_ARG_CHECK(N == 0 || Xk != nullptr);
   } else {
-    FRODO_ARG_CHECK(Kmat != nullptr && (N == 0 || (meas_k && valid_meas_k)));
+    FRODO_ARG_CHECK(Kmat != nullptr);
+    FRODO_ARG_CHECK(N == 0 || (params->raw_calib ? Xk != nullptr : (meas_k && valid_meas_k)));
     FRODO_ARG_CHECK(params->height > 0 && params->width > 0);
+    FRODO_ARG_CHECK(!params->raw_calib || (long long)params->height * params->width == N);
   }
   FRODO_ARG_CHECK(workspace != nullptr && workspace_bytes >= track_workspace_bytes(N));
   FRODO_ARG_CHECK((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0);

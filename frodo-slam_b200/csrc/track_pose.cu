@@ -55,6 +55,7 @@ struct TrackArgs {
   float* overflow;         // [8][N] records of the points that do not fit in shared memory
   int N, per, cap;
   int mode, max_iters;
+  int raw_calib, width;    // calib: build the measurement from the raw pointmaps in the prologue
   float sa_inv, sb_inv, huber_k, rel_error, delta_norm;
   float fx, fy, cx, cy, ulo, uhi, vlo, vhi, z_eps;
 };
@@ -264,9 +265,10 @@ __global__ void __launch_bounds__(kTrkThreads, 1) track_pose_kernel(const TrackA
       m[u] = a.idx ? a.idx[n] : (long long)n;
       ok[u] = a.valid[n] != 0;
       q[u] = a.Qk[n];
-      const float* src = (MODE == FRODO_GN_RAYS ? a.Xk : a.meas) + (size_t)n * 3;
+      const bool raw = MODE != FRODO_GN_RAYS && a.raw_calib != 0;
+      const float* src = ((MODE == FRODO_GN_RAYS || raw) ? a.Xk : a.meas) + (size_t)n * 3;
       km[u][0] = src[0]; km[u][1] = src[1]; km[u][2] = src[2];
-      if (MODE != FRODO_GN_RAYS) ok[u] = ok[u] && a.valid_meas[n] != 0;
+      if (MODE != FRODO_GN_RAYS && !raw) ok[u] = ok[u] && a.valid_meas[n] != 0;
     }
 #pragma unroll
     for (int u = 0; u < kPro; ++u) {
@@ -280,6 +282,23 @@ __global__ void __launch_bounds__(kTrkThreads, 1) track_pose_kernel(const TrackA
       const int n = start + p;
       float r[kRec];
       r[0] = xf[u][0]; r[1] = xf[u][1]; r[2] = xf[u][2];
+      if (MODE != FRODO_GN_RAYS && a.raw_calib != 0) {
+        // the calibrated branch of get_points_poses (tracker.py:383-393): both points are put
+        // back on their own pixel ray at their depth (constrain_points_to_ray / backproject,
+        // geometry.py:37-42,107-116), the keyframe's measurement is (u, v, log z)
+        const int mf = (int)m[u];
+        const float uf = (float)(mf % a.width), vf = (float)(mf / a.width);
+        const float zf = xf[u][2];
+        r[0] = zf * __fdiv_rn(uf - a.cx, a.fx);
+        r[1] = zf * __fdiv_rn(vf - a.cy, a.fy);
+        r[2] = zf * 1.0f;
+        const float zk = km[u][2];
+        const bool vz = zk > a.z_eps;
+        ok[u] = ok[u] && vz;
+        km[u][0] = (float)(n % a.width);
+        km[u][1] = (float)(n / a.width);
+        km[u][2] = vz ? logf(zk) : 0.0f;
+      }
       if (MODE == FRODO_GN_RAYS) {
         const float k0 = km[u][0], k1 = km[u][1], k2 = km[u][2];
         const float d = sqrtf(k0 * k0 + k1 * k1 + k2 * k2);
@@ -504,6 +523,7 @@ int launch_track_pose(const frodo_track_params& prm, const float* Xf, const int6
   if (a.per < 1) a.per = 1;
   a.cap = a.per < kMaxSmemPts ? a.per : kMaxSmemPts;
   a.mode = prm.mode; a.max_iters = prm.max_iters;
+  a.raw_calib = prm.raw_calib; a.width = prm.width > 0 ? prm.width : 1;
   a.sa_inv = 1.0f / prm.sigma_a; a.sb_inv = 1.0f / prm.sigma_b;
   a.huber_k = prm.huber; a.rel_error = prm.rel_error; a.delta_norm = prm.delta_norm;
   a.fx = a.fy = 1.0f; a.cx = a.cy = 0.0f;

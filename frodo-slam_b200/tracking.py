@@ -92,15 +92,21 @@ def track_pose(mode, Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k=None, valid_meas_k=
     prm.max_iters = int(c["max_iters"])
     prm.rel_error = float(c["rel_error"])
     prm.delta_norm = float(c["delta_norm"])
-    prm.height = prm.width = prm.pixel_border = 0
+    prm.height = prm.width = prm.pixel_border = prm.raw_calib = 0
     prm.z_eps = 0.0
     if mode == "rays":
         prm.sigma_a, prm.sigma_b = float(c["sigma_ray"]), float(c["sigma_dist"])
         Xk = _arr(Xk, "Xk", torch.float32, N, 3, dev)
     else:
         prm.sigma_a, prm.sigma_b = float(c["sigma_pixel"]), float(c["sigma_depth"])
-        meas_k = _arr(meas_k, "meas_k", torch.float32, N, 3, dev)
-        valid_meas_k = _arr(valid_meas_k, "valid_meas_k", torch.bool, N, 1, dev)
+        if meas_k is None:  # raw pointmaps: the kernel builds the measurement (raw_calib)
+            prm.raw_calib = 1
+            Xk = _arr(Xk, "Xk", torch.float32, N, 3, dev)
+            if int(img_size[0]) * int(img_size[1]) != N:
+                raise RuntimeError("raw calibrated tracking needs img_size[0] * img_size[1] == N")
+        else:
+            meas_k = _arr(meas_k, "meas_k", torch.float32, N, 3, dev)
+            valid_meas_k = _arr(valid_meas_k, "valid_meas_k", torch.bool, N, 1, dev)
         K = _arr(K, "K", torch.float32, 3, 3, dev)
         prm.height, prm.width = int(img_size[0]), int(img_size[1])
         prm.pixel_border = int(c["pixel_border"])
@@ -118,9 +124,10 @@ def track_pose(mode, Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k=None, valid_meas_k=
         nbytes = lib.frodo_track_workspace_bytes(N)
         ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         _lib.check(lib.frodo_track_pose(
-            ctypes.byref(prm), _ptr(Xf), _ptr(idx_f2k), _ptr(Xk) if mode == "rays" else None,
-            _ptr(Qk), _ptr(valid), _ptr(meas_k) if mode == "calib" else None,
-            _ptr(valid_meas_k) if mode == "calib" else None, _ptr(K) if mode == "calib" else None,
+            ctypes.byref(prm), _ptr(Xf), _ptr(idx_f2k),
+            _ptr(Xk) if (mode == "rays" or prm.raw_calib) else None,
+            _ptr(Qk), _ptr(valid), _ptr(meas_k) if (mode == "calib" and not prm.raw_calib) else None,
+            _ptr(valid_meas_k) if (mode == "calib" and not prm.raw_calib) else None, _ptr(K) if mode == "calib" else None,
             _ptr(Tf), _ptr(Tk), N, _ptr(out_f), _ptr(out_rel), _ptr(info), _ptr(costs), _ptr(ws),
             nbytes, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
     return dict(T_WCf=out_f, T_CkCf=out_rel, info=info, costs=costs)
@@ -148,7 +155,10 @@ def opt_pose_ray_dist_sim3(Xf, Xk, T_WCf, T_WCk, Qk, valid, cfg=None, idx_f2k=No
 
 def opt_pose_calib_sim3(Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K, img_size,
                         cfg=None, idx_f2k=None):
-    """tracker.py:467-517 (``Xk`` is unused there too: the measurement is ``meas_k``)."""
+    """tracker.py:467-517 (``Xk`` is unused there too: the measurement is ``meas_k``).
+    With ``meas_k=None`` the RAW pointmaps go in (``Xf`` the frame's own ``[H*W,3]`` with
+    ``idx_f2k``, ``Xk`` the keyframe's) and the kernel's prologue does the calibrated branch of
+    ``get_points_poses`` (tracker.py:383-393) itself."""
     r = track_pose("calib", Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K, img_size,
                    idx_f2k=idx_f2k, cfg=cfg)
     return _finish(r, T_WCf)

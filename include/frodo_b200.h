@@ -347,6 +347,10 @@ typedef struct frodo_track_params {
   int width;
   int pixel_border;
   float z_eps;
+  int raw_calib; /* calib only, non-zero: Xf and Xk are the RAW pointmaps [H*W,3]; the kernel does
+                    the calibrated branch of get_points_poses itself (tracker.py:383-393:
+                    constrain_points_to_ray + meas_k = (u, v, log z), valid_meas_k = z > z_eps)
+                    and meas_k / valid_meas_k are ignored (may be NULL) */
 } frodo_track_params;
 
 size_t frodo_track_workspace_bytes(int N);

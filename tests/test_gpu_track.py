@@ -227,3 +227,19 @@ def test_zero_iterations_and_argument_errors(ft, dev):
     with pytest.raises(RuntimeError):  # non-contiguous
         strided = _t(np.zeros((c["Xk"].shape[0], 6), np.float32), dev)[:, ::2]
         ft.track_pose("rays", _t(c["Xf"], dev), strided, _t(c["T_WCf"], dev), _t(c["T_WCk"], dev), _t(c["Qk"], dev), _t(c["valid"], dev))
+
+
+def test_calib_from_raw_pointmaps_equals_torch_glue(ft, dev):
+    """raw_calib: the prologue does constrain_points_to_ray + meas_k (tracker.py:383-393) itself."""
+    for (H, W, seed) in ((48, 64, 11), (37, 53, 12)):
+        c = _case(H, W, seed, 0.01)
+        a = _gpu(ft, "calib", c, dev)  # torch glue (calib_measurements) + kernel
+        r = ft.track_pose("calib", _t(c["Xf_all"], dev), _t(c["Xk"], dev), _t(c["T_WCf"], dev),
+                          _t(c["T_WCk"], dev), _t(c["Qk"], dev), _t(c["valid"], dev), None, None,
+                          _t(c["K"], dev), (H, W), idx_f2k=_t(c["idx_f2k"], dev), cfg=TP)
+        it, failed = r["info"].tolist()
+        assert failed == 0 and it == a["iters"]
+        assert np.abs(r["T_WCf"].cpu().numpy() - a["T_WCf"]).max() < 1e-6
+        assert np.abs(r["costs"].cpu().numpy()[:it] / a["costs"] - 1).max() < 1e-6
+        _agree(dict(T_WCf=r["T_WCf"].cpu().numpy(), T_CkCf=r["T_CkCf"].cpu().numpy(), iters=it,
+                    status=failed, costs=r["costs"].cpu().numpy()[:it]), _oracle("calib", c))
