@@ -41,4 +41,20 @@ for _ in range(2):
                            mp["convergence_thresh"])
     be.refine_matches(D11, D21, p.long(), mp["radius"], mp["dilation_max"])
 torch.cuda.synchronize()
+# the matching pipeline in one call (prep, occlusion, casts, finish) and the quality glue
+from frodo_slam_b200 import matching as fm, tracking  # noqa: E402
+X11, X21 = d["X11"].float().contiguous(), d["X21"].float().contiguous()
+D11f, D21f = d["D11"].float().contiguous(), d["D21"].float().contiguous()
+idx, valid = fm.match(X11, X21, D11f, D21f, cfg=mp)
+Qs = torch.rand(B, H * W, 1, device=dev) * 3
+fm.match_quality(Qs, Qs.clone(), idx, valid.reshape(B, H * W, 1), 1.5, Qs, Qs, 0.0)
+torch.cuda.synchronize()
+del d, X11, X21, D11f, D21f, D11, D21
+# the tracker's pose solve
+c = synth.tracking_case(H, W, seed=7)
+t = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in c.items()}
+for _ in range(2):
+    tracking.track_pose("rays", t["Xf_all"], t["Xk"], t["T_WCf"], t["T_WCk"], t["Qk"], t["valid"],
+                        idx_f2k=t["idx_f2k"], cfg=synth.TRACK_PARAMS)
+torch.cuda.synchronize()
 print("prof_ops done")
