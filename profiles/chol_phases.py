@@ -56,6 +56,11 @@ for k in range(Tc):
 print({k: round(float(v), 2) for k, v in tot.items()})
 print(f"back substitution   {us(st[2 + 3 * Tc], st[3 + 3 * Tc]):8.2f} us")
 print(f"total               {us(st[0], st[3 + 3 * Tc]):8.2f} us")
+if st[116] > 0:
+    print(f"pose update (dx, retraction)  {us(st[3 + 3 * Tc], st[116]):8.2f} us")
+    wall = (st[119] - st[118]) / 1e3
+    print(f"wall clock (globaltimer) start -> end of kernel body {wall:8.2f} us  => SM clock "
+          f"{(st[116] - st[0]) / wall:7.1f} MHz during the kernel")
 # cycles accumulated by every diagonal-tile call since the workspace was allocated (3 solves)
 if st[120] > 0:
     calls = 3 * Tc
