@@ -38,7 +38,9 @@ int launch_iter_proj(const float* rays, const float* pts, const float* p_init, f
                      float lambda_init, float cost_thresh, cudaStream_t s);
 int launch_refine_f16(const __half* D11, const __half* D21, const int64_t* p1, int64_t* p1_new,
                       __half* scores, int B, int H, int W, int N, int F, int radius, int dil,
-                      cudaStream_t s);
+                      cudaStream_t s, const float* D21_f32 = nullptr);
+bool refine_f16_takes_tile_kernel(const void* D11, const void* D21, const void* p1,
+                                  const void* p1_new, int B, int H, int W, int N, int F);
 int launch_refine_f32(const float* D11, const float* D21, const int64_t* p1, int64_t* p1_new,
                       float* scores, int B, int H, int W, int N, int F, int radius, int dil,
                       cudaStream_t s);

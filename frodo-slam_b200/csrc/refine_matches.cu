@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(kTileThreads, 1)
 refine_f16_tile_kernel(const __half* __restrict__ D11, const __half* __restrict__ D21,
                        const int64_t* __restrict__ p1, int64_t* __restrict__ p1_new,
                        __half* __restrict__ scores, int H, int W, int radius, int dil_max,
-                       int cap_px) {
+                       int cap_px, const float* __restrict__ D21_f32) {
   extern __shared__ __align__(128) unsigned char tile[];
   __shared__ uint64_t bar;
   __shared__ int box[4];  // min u, max u, min v, max v of the centres that can reach the image
@@ -266,7 +266,17 @@ refine_f16_tile_kernel(const __half* __restrict__ D11, const __half* __restrict_
   }
 
   __half2 q2[F / 2];
-  if (reach) {
+  if (reach && D21_f32 != nullptr) {
+    // fp32 query descriptors (frodo_match): D21.half() of matching.py:80 done here, round to
+    // nearest even per element as the cast kernel does, so the separate pass over D21 disappears
+    const float4* qp = reinterpret_cast<const float4*>(D21_f32 + t * F);
+#pragma unroll
+    for (int m = 0; m < F / 4; ++m) {
+      const float4 xq = __ldg(qp + m);
+      q2[2 * m] = __floats2half2_rn(xq.x, xq.y);
+      q2[2 * m + 1] = __floats2half2_rn(xq.z, xq.w);
+    }
+  } else if (reach) {
     const uint4* qp = reinterpret_cast<const uint4*>(D21 + t * F);
 #pragma unroll
     for (int blk = 0; blk < F / 8; ++blk) {
@@ -428,15 +438,31 @@ refine_f32_kernel(const float* __restrict__ D11, const float* __restrict__ D21,
 
 }  // namespace
 
+// True when launch_refine_f16 takes the tile-staged kernel for these arguments: only that kernel
+// can read fp32 query descriptors (D21_f32), so frodo_match asks before skipping the D21 cast.
+bool refine_f16_takes_tile_kernel(const void* D11, const void* D21, const void* p1,
+                                  const void* p1_new, int B, int H, int W, int N, int F) {
+  const bool aligned = ((reinterpret_cast<uintptr_t>(D11) | reinterpret_cast<uintptr_t>(D21) |
+                         reinterpret_cast<uintptr_t>(p1) | reinterpret_cast<uintptr_t>(p1_new)) &
+                        15) == 0;
+  return aligned && N == H * W && (F == 24 || F == 16 || F == 32) && B <= 65535;
+}
+
 int launch_refine_f16(const __half* D11, const __half* D21, const int64_t* p1, int64_t* p1_new,
                       __half* scores, int B, int H, int W, int N, int F, int radius, int dil,
-                      cudaStream_t s) {
+                      cudaStream_t s, const float* D21_f32) {
   if (B == 0 || N == 0) return FRODO_OK;
   dim3 grid((N + 127) / 128, B);
   const bool aligned = ((reinterpret_cast<uintptr_t>(D11) | reinterpret_cast<uintptr_t>(D21) |
                          reinterpret_cast<uintptr_t>(p1) | reinterpret_cast<uintptr_t>(p1_new)) &
                         15) == 0;
-  if (aligned && N == H * W && (F == 24 || F == 16 || F == 32) && B <= 65535) {
+  const bool tile = refine_f16_takes_tile_kernel(D11, D21_f32 ? (const void*)D21_f32 : (const void*)D21,
+                                                 p1, p1_new, B, H, W, N, F);
+  if (D21_f32 != nullptr && !tile) {
+    set_error("refine_matches: fp32 query descriptors need the tile-staged kernel");
+    return FRODO_ERR_ARG;
+  }
+  if (tile) {
     dim3 tgrid((W + kTilePatchW - 1) / kTilePatchW, (H + kTilePatchH - 1) / kTilePatchH, B);
     const int cap_px = kTileSmemBytes / (F * 2);
 #define FRODO_TILE_LAUNCH(FF, RR)                                                               \
@@ -449,7 +475,7 @@ int launch_refine_f16(const __half* D11, const __half* D21, const int64_t* p1, i
       attr_set = true;                                                                          \
     }                                                                                           \
     refine_f16_tile_kernel<FF, RR><<<tgrid, kTileThreads, kTileSmemBytes, s>>>(                 \
-        D11, D21, p1, p1_new, scores, H, W, radius, dil, cap_px);                               \
+        D11, D21, p1, p1_new, scores, H, W, radius, dil, cap_px, D21_f32);                      \
   } while (0)
     if (F == 24 && radius == 3) FRODO_TILE_LAUNCH(24, 3);
     else if (F == 24) FRODO_TILE_LAUNCH(24, 0);
