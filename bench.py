@@ -310,6 +310,46 @@ def cpu_baseline_gn(g_np, seconds=12.0):
                       f"(solve excluded), extrapolated x{E / ns:.0f}"}
 
 
+def run_other_configs(dev, be, iters, quiet=False):
+    """The smaller graphs of BASELINE.json: configs[1] (8-keyframe sliding window, E = 24,
+    gauss_newton_rays) and configs[3] (32 keyframes, E = 128, gauss_newton_calib, TUM-like
+    intrinsics) at 512x384, through the backend module `be` (ours or the reference's): iters/s of
+    a 10-iteration call with delta_thresh = 0, inputs resident on the device."""
+    from frodo_slam_b200 import synth
+    gp = synth.GN_PARAMS
+    out = {}
+    for name, cfgname, mode in (("window8_rays", "window8", "rays"), ("calib32", "calib32", "calib")):
+        K, und = synth.graph_edges(cfgname)
+        g = synth.keyframe_graph(K, H_IMG, W_IMG, und, seed=1, device=dev)
+        T0 = g["Twc"].clone()
+
+        def call():
+            T = T0.clone()
+            if mode == "rays":
+                be.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"],
+                                     g["valid_match"], g["Q"], gp["sigma_ray"], gp["sigma_dist"],
+                                     gp["C_conf"], gp["Q_conf"], gp["num_fix"], iters, 0.0)
+            else:
+                be.gauss_newton_calib(T, g["Xs"], g["Cs"], g["K"], g["ii"], g["jj"],
+                                      g["idx_ii2jj"], g["valid_match"], g["Q"], H_IMG, W_IMG,
+                                      gp["pixel_border"], gp["depth_eps"], gp["sigma_pixel"],
+                                      gp["sigma_depth"], gp["C_conf"], gp["Q_conf"], iters, 0.0)
+
+        n = 5
+        if quiet:
+            with _QuietStdout():
+                ms = timed_steps(call, n, 2)
+        else:
+            ms = timed_steps(call, n, 2)
+        E = int(g["ii"].shape[0])
+        out[name] = {"keyframes": K, "directed_edges": E, "iters_per_s": n * iters / (ms * 1e-3),
+                     "ms_per_call": ms / n,
+                     "algorithmic_gb_per_iteration": 45 * N_PTS * E / 1e9}
+        del g
+        torch.cuda.empty_cache()
+    return out
+
+
 def run_tracking(dev):
     """The tracker's frame-to-keyframe pose solve (tracker.py:397-517) on one
     512x384 frame through frodo_slam_b200.tracking (one persistent cooperative kernel): time per
@@ -592,6 +632,7 @@ def main_ours(args):
     if g_np is not None:
         cpu = cpu_baseline_gn(g_np)
     tracking = run_tracking(dev) if (world == 1 and not args.no_matching) else None
+    other = run_other_configs(dev, be, iters) if (world == 1 and not args.no_matching) else None
 
     if rank == 0:
         line = {
@@ -608,6 +649,7 @@ def main_ours(args):
             "gpu_launches": args.steps * (1 + 3 * iters),  # pack + (accumulate, assemble, solve)/iter
             "matching": matching,
             "tracking": tracking,
+            "other_configs": other,
         }
         print(json.dumps(line))
     if world > 1:
@@ -710,6 +752,7 @@ def main_reference(args):
                          be=ref)
         m["gpu_launches"] = None
         line["matching"] = m
+        line["other_configs"] = run_other_configs(dev, ref, iters, quiet=True)
     print(json.dumps(line))
 
 

@@ -13,7 +13,7 @@ from frodo_slam_b200.backends import _ptr, _stream  # noqa: E402
 
 dev = torch.device("cuda:0")
 gp = synth.GN_PARAMS
-K, und = synth.graph_edges("loop64")
+K, und = synth.graph_edges(os.environ.get("FRODO_TL_GRAPH", "loop64"))
 H, W = 384, 512
 g = synth.keyframe_graph(K, H, W, und, seed=1, device=dev)
 E, N = g["ii"].shape[0], H * W
