@@ -203,6 +203,85 @@ solve_retract_kernel(double* __restrict__ A, float* __restrict__ Twc, float* __r
 }
 
 
+// ---------------------------------------------------------------------------------------
+// Small systems (n <= 63: up to 9 free keyframes, i.e. the sliding-window local optimisation of
+// the fork's tracker, tracker.py:27-60): the cluster machinery of gn_chol_cluster.cu (cluster
+// barriers, L2 scratch, bulk copies) costs ~50 us for two 32x32 tiles.  Here the whole
+// (n+1) x n system [H ; g^T] sits in the shared memory of one CTA (row pitch 65 doubles:
+// column accesses are conflict-free) and a right-looking factorisation runs with two block
+// barriers per pivot: every thread forms 1/sqrt(a_jj) redundantly, 64 threads scale column j,
+// a 16 x 16 thread grid applies the rank-1 update.  Rolled loops on purpose: a fully unrolled
+// register-resident variant (row t in the registers of thread t) was 2x SLOWER than the cluster
+// path -- 300 KB of straight-line code executed once is bound by instruction fetch.
+// The rhs rides along as row n (y = L^-1 g); the back substitution is column-oriented.
+constexpr int kSmallN = 63;
+constexpr int kSmallThreads = 256;
+constexpr int kSmallLd = 65;
+
+__global__ void __launch_bounds__(kSmallThreads)
+solve_small_kernel(const double* __restrict__ A, float* __restrict__ Twc, float* __restrict__ dx,
+                   int n, int K, int num_fix, float delta_thresh, int32_t* __restrict__ done,
+                   int32_t* __restrict__ info, const int32_t* __restrict__ pose_rows) {
+  if (done != nullptr && *done != 0) return;
+  __shared__ double M[(kSmallN + 1) * kSmallLd];  // rows 0..n, lower triangle used
+  __shared__ double lcol[kSmallN + 1];            // column j of L during step j
+  __shared__ double s_inv[kSmallN + 1];
+  __shared__ double xs[kSmallN + 1];
+  const int t = threadIdx.x;
+  const int rows = n + 1;
+  // coalesced load, 4 independent loads in flight per thread
+  for (int r0 = 0; r0 < rows; r0 += 4 * (kSmallThreads / 64)) {
+    double v[4];
+    const int c = t & 63, rr = t >> 6;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int r = r0 + rr + u * (kSmallThreads / 64);
+      v[u] = (r < rows && c < n) ? A[(size_t)r * n + c] : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int r = r0 + rr + u * (kSmallThreads / 64);
+      if (r < rows && c < n) M[r * kSmallLd + c] = v[u];
+    }
+  }
+  __syncthreads();
+  bool fail = false;
+  const int ty = t >> 4, tx = t & 15;
+  for (int j = 0; j < n; ++j) {
+    const double d = M[j * kSmallLd + j];
+    fail = !(d > 0.0) || !isfinite(d);
+    if (fail) break;  // uniform: every thread read the same pivot
+    const double inv = rsqrt(d);
+    if (t >= j && t < rows) {
+      const double l = (t == j) ? d * inv : M[t * kSmallLd + j] * inv;
+      lcol[t] = l;
+      if (t == j) s_inv[j] = inv;
+    }
+    __syncthreads();
+    if (t >= j && t < rows) M[t * kSmallLd + j] = lcol[t];
+    for (int r = j + 1 + ty; r < rows; r += 16) {
+      const double lr = lcol[r];
+      for (int c = j + 1 + tx; c <= r && c < n; c += 16)
+        M[r * kSmallLd + c] = fma(-lr, lcol[c], M[r * kSmallLd + c]);
+    }
+    __syncthreads();
+  }
+  const int nopt = K - num_fix;
+  if (fail) {
+    fail_update<kSmallThreads>(dx, nopt, delta_thresh, done, info);
+    return;
+  }
+  // x = L^-T y with y = row n; thread i < n keeps y_i, x_j is broadcast through xs
+  double yi = t < n ? M[n * kSmallLd + t] : 0.0;
+  for (int j = n - 1; j >= 0; --j) {
+    if (t == j) xs[j] = yi * s_inv[j];
+    __syncthreads();
+    if (t < j) yi = fma(-M[j * kSmallLd + t], xs[j], yi);
+  }
+  __syncthreads();
+  finish_update<kSmallThreads>(xs, Twc, dx, n, nopt, num_fix, delta_thresh, done, info, pose_rows);
+}
+
 }  // namespace
 
 int launch_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fix,
@@ -210,6 +289,12 @@ int launch_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fi
                             cudaStream_t s, const int32_t* pose_rows) {
   const int n = 7 * (K - num_fix);
   if (n <= 0) return FRODO_OK;
+  if (n <= kSmallN) {  // sliding-window sized systems: register-resident single-CTA solve
+    solve_small_kernel<<<1, kSmallThreads, 0, s>>>(Hg, Twc, dx, n, K, num_fix, delta_thresh, done,
+                                                   info, pose_rows);
+    FRODO_CUDA_TRY(cudaGetLastError());
+    return FRODO_OK;
+  }
   // fast path: cluster-resident tiled Cholesky (gn_chol_cluster.cu)
   int handled = 0;
   const int rc = launch_chol_cluster(Hg, Twc, dx, K, num_fix, delta_thresh, done, info,
