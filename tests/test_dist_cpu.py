@@ -85,3 +85,13 @@ def test_allreduce_of_edge_shards_world2():
     for _, _, _, rel, same in res:
         assert rel < 1e-12  # fp64 sums of disjoint edge sets in a different order
         assert same         # identical inputs to the replicated solve on every rank
+
+
+def test_peer_exchange_is_cuda_only_and_can_be_disabled(monkeypatch):
+    """The peer-memory exchange (csrc/peer_reduce.cu) is only set up for CUDA devices; on other
+    devices, or with FRODO_PEER_REDUCE=0, the driver keeps the collective (NCCL / gloo)."""
+    import torch
+    from frodo_slam_b200 import dist as fdist
+    assert fdist._peer_state(100, torch.device("cpu"), None) is None
+    monkeypatch.setenv("FRODO_PEER_REDUCE", "0")
+    assert fdist._peer_state(100, torch.device("cuda", 0), None) is None
