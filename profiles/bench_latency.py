@@ -28,7 +28,7 @@ def t(fn, n=30):
     return e0.elapsed_time(e1) / n * 1e3
 
 
-for B in (1, 2, 8):
+for B in [int(x) for x in os.environ.get("FRODO_LAT_B", "1,2,8").split(",")]:
     d = synth.matching_pairs(B, H, W, seed=0, device=dev)
     X11, X21 = d["X11"].float().contiguous(), d["X21"].float().contiguous()
     D11, D21 = d["D11"].float().contiguous(), d["D21"].float().contiguous()

@@ -265,3 +265,26 @@ def test_gn_rays_odom_vs_reference(be, dev, ref_backend, capfd):
         if iters == 1:
             assert rel_err(da, db) < GN_TOL
     capfd.readouterr()
+
+
+def test_refine_patch_variants_agree_bitwise(be, dev, monkeypatch):
+    """refine_matches runs 16x16 patches (two CTAs per SM) for F <= 24 and keeps the 32x32 kernel
+    for F = 32; both must give the same bits.  FRODO_REFINE_PATCH forces the variant."""
+    from frodo_slam_b200 import synth
+    mp = synth.MATCH_PARAMS
+    B, H, W = 2, 384, 512
+    d = synth.matching_pairs(B, H, W, seed=4, device=dev)
+    rays, pts, p0 = synth.prep_for_iter_proj(d["X11"], d["X21"])
+    p1 = be.iter_proj(rays, pts, p0, mp["max_iter"], mp["lambda_init"], mp["convergence_thresh"])[0].long()
+    g = torch.Generator(device=dev).manual_seed(1)
+    p1 = p1 + torch.randint(-6, 7, p1.shape, device=dev, generator=g)  # off-box candidates too
+    D11 = d["D11"].half().contiguous()
+    D21 = d["D21"].half().reshape(B, H * W, -1).contiguous()
+    out = {}
+    for v in ("16", "32"):
+        monkeypatch.setenv("FRODO_REFINE_PATCH", v)
+        pn, sc = be.refine_matches(D11, D21, p1, mp["radius"], mp["dilation_max"])
+        torch.cuda.synchronize()
+        out[v] = (pn.clone(), sc.clone())
+    assert torch.equal(out["16"][0], out["32"][0])
+    assert torch.equal(out["16"][1].view(torch.int16), out["32"][1].view(torch.int16))
