@@ -20,6 +20,19 @@ int cuda_fail(cudaError_t e, const char* what) {
   return FRODO_ERR_CUDA;
 }
 
+int num_sms() {
+  static int cache[kMaxDevices] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return kNumSMs;
+  if (cache[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = kNumSMs;
+    cache[dev] = n;
+  }
+  return cache[dev];
+}
+
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 size_t gn_carve_workspace(void* base, int K, int E, int N, GnWorkspace* ws) {
@@ -89,6 +102,8 @@ int frodo_refine_matches_f16(const void* D11, const void* D21, const int64_t* p1
                            p1_new, static_cast<__half*>(max_scores), B, H, W, N, F, radius,
                            dilation_max, static_cast<cudaStream_t>(stream));
 }
+
+int frodo_set_refine_patch(int patch) { return refine_forced_patch(patch < 0 ? 0 : patch); }
 
 int frodo_refine_matches_f32(const float* D11, const float* D21, const int64_t* p1,
                              int64_t* p1_new, float* max_scores, int B, int H, int W, int N, int F,

@@ -13,7 +13,28 @@
 
 namespace frodo {
 
-constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
+constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs (compile-time model; see num_sms())
+constexpr int kMaxDevices = 64;
+
+// One-time per-DEVICE setup guard.  Function attributes (dynamic shared memory size, cluster
+// size) belong to the device's context, so a process that drives several GPUs must set them
+// once on each; a second thread racing here repeats an idempotent call, nothing worse.
+struct PerDeviceOnce {
+  volatile unsigned char set[kMaxDevices] = {};
+  // Returns the current device in *dev (-1 on error) and whether setup is still needed there.
+  bool needed(int* dev) {
+    int d = -1;
+    if (cudaGetDevice(&d) != cudaSuccess) d = -1;
+    *dev = d;
+    return d < 0 || d >= kMaxDevices || !set[d];
+  }
+  void mark(int dev) {
+    if (dev >= 0 && dev < kMaxDevices) set[dev] = 1;
+  }
+};
+
+// SM count of the current device (cached per device; 148 on a full B200, fewer on a MIG slice).
+int num_sms();
 
 void set_error(const char* fmt, ...);
 int cuda_fail(cudaError_t e, const char* what);
@@ -39,6 +60,7 @@ int launch_iter_proj(const float* rays, const float* pts, const float* p_init, f
 int launch_refine_f16(const __half* D11, const __half* D21, const int64_t* p1, int64_t* p1_new,
                       __half* scores, int B, int H, int W, int N, int F, int radius, int dil,
                       cudaStream_t s, const float* D21_f32 = nullptr);
+int refine_forced_patch(int set);
 bool refine_f16_takes_tile_kernel(const void* D11, const void* D21, const void* p1,
                                   const void* p1_new, int B, int H, int W, int N, int F);
 int launch_refine_f32(const float* D11, const float* D21, const int64_t* p1, int64_t* p1_new,

@@ -987,16 +987,17 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
   // calib additionally needs N < 2^32 target pixels, which N as an int guarantees
   if (XC != nullptr && (N % 16) == 0 && aligned16 &&
       (prm.mode != FRODO_GN_CALIB || Kmat != nullptr)) {
-    static bool attr_set = false;
+    static PerDeviceOnce once;
+    int dev;
     const size_t smem = (size_t)kRaysSmemBytes;
-    if (!attr_set) {
+    if (once.needed(&dev)) {
       FRODO_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_packed_kernel<FRODO_GN_RAYS>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       FRODO_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_packed_kernel<FRODO_GN_POINTS>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       FRODO_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_packed_kernel<FRODO_GN_CALIB>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr_set = true;
+      once.mark(dev);
     }
     const float4* xc = reinterpret_cast<const float4*>(XC);
     const float4* xp = xc + (size_t)K * N;

@@ -172,11 +172,12 @@ int launch_gn_edge_index(const int64_t* ii, const int64_t* jj, int E, int32_t* i
     set_error("edge index: more than %d edges are not supported", (200 * 1024 / 12) / 2);
     return FRODO_ERR_ARG;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce once;
+  int dev;
+  if (once.needed(&dev)) {
     FRODO_CUDA_TRY(cudaFuncSetAttribute(edge_index_kernel,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_set = true;
+    once.mark(dev);
   }
   edge_index_kernel<<<1, kIdxThreads, need, s>>>(ii, jj, E, P, nullptr, nullptr, ii_row, jj_row,
                                                   n_unique, 1, q_ids, nq, q_rows);

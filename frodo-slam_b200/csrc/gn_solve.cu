@@ -301,12 +301,13 @@ int launch_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fi
                                      chol_scratch, &handled, s, pose_rows);
   if (rc != FRODO_OK || handled) return rc;
   // fallback for systems that do not fit the cluster's shared memory
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce once;
+  int dev;
+  if (once.needed(&dev)) {
     FRODO_CUDA_TRY(cudaFuncSetAttribute(solve_retract_kernel,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)sizeof(SolveSmem)));
-    attr_set = true;
+    once.mark(dev);
   }
   solve_retract_kernel<<<1, kSolveThreads, sizeof(SolveSmem), s>>>(Hg, Twc, dx, n, K, num_fix,
                                                                   delta_thresh, done, info,

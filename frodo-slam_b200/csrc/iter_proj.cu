@@ -325,12 +325,13 @@ int launch_iter_proj(const float* rays, const float* pts, const float* p_init, f
                        (reinterpret_cast<uintptr_t>(p_init) & 7) == 0 &&
                        (reinterpret_cast<uintptr_t>(p_new) & 7) == 0;
   if (N == H * W && (W % 4) == 0 && W >= 4 && H >= 3 && aligned && B <= 65535) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce once;
+    int dev;
+    if (once.needed(&dev)) {
       FRODO_CUDA_TRY(cudaFuncSetAttribute(iter_proj_window_kernel,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           kWinSmemBytes));
-      attr_set = true;
+      once.mark(dev);
     }
     dim3 wgrid((W + kWinPatchW - 1) / kWinPatchW, (H + kWinPatchH - 1) / kWinPatchH, B);
     iter_proj_window_kernel<<<wgrid, kWinThreads, kWinSmemBytes, s>>>(

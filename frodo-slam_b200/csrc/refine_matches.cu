@@ -458,6 +458,18 @@ bool refine_f16_takes_tile_kernel(const void* D11, const void* D21, const void* 
   return aligned && N == H * W && (F == 24 || F == 16 || F == 32) && B <= 65535;
 }
 
+// Patch-size override of the tile-staged kernel: 0 = automatic, 16 or 32.  The environment
+// variable FRODO_REFINE_PATCH seeds it once per process; frodo_set_refine_patch() changes it at
+// run time (tests compare the two variants bit for bit).  set < 0 only reads.
+int refine_forced_patch(int set) {
+  static int value = [] {
+    const char* f = getenv("FRODO_REFINE_PATCH");
+    return f == nullptr ? 0 : (f[0] == '1' ? 16 : (f[0] == '3' ? 32 : 0));
+  }();
+  if (set >= 0) value = (set == 16 || set == 32) ? set : 0;
+  return value;
+}
+
 int launch_refine_f16(const __half* D11, const __half* D21, const int64_t* p1, int64_t* p1_new,
                       __half* scores, int B, int H, int W, int N, int F, int radius, int dil,
                       cudaStream_t s, const float* D21_f32) {
@@ -477,22 +489,22 @@ int launch_refine_f16(const __half* D11, const __half* D21, const int64_t* p1, i
                               ((H + kTilePatchH - 1) / kTilePatchH) * B;
     (void)tiles32;
     bool small_grid = F <= 24;  // "small" = the 16x16, two-CTAs-per-SM variant
-    if (const char* force = getenv("FRODO_REFINE_PATCH")) {  // test switch: 16 or 32
-      if (force[0] == '1' && F <= 24) small_grid = true;
-      if (force[0] == '3') small_grid = false;
-    }
+    const int forced_patch = refine_forced_patch(-1);  // tuning/test switch, see below
+    if (forced_patch == 16 && F <= 24) small_grid = true;
+    if (forced_patch == 32) small_grid = false;
     const int pw = small_grid ? kSmallPatch : kTilePatchW, ph = small_grid ? kSmallPatch : kTilePatchH;
     const int smem_bytes = small_grid ? kSmallSmemBytes : kTileSmemBytes;
     dim3 tgrid((W + pw - 1) / pw, (H + ph - 1) / ph, B);
     const int cap_px = smem_bytes / (F * 2);
 #define FRODO_TILE_LAUNCH_P(FF, RR, PWW, PHH)                                                   \
   do {                                                                                          \
-    static bool attr_set = false;                                                               \
-    if (!attr_set) {                                                                            \
+    static PerDeviceOnce once;                                                                  \
+    int dev_;                                                                                   \
+    if (once.needed(&dev_)) {                                                                   \
       FRODO_CUDA_TRY(cudaFuncSetAttribute(refine_f16_tile_kernel<FF, RR, PWW, PHH>,             \
                                           cudaFuncAttributeMaxDynamicSharedMemorySize,          \
                                           smem_bytes));                                         \
-      attr_set = true;                                                                          \
+      once.mark(dev_);                                                                          \
     }                                                                                           \
     refine_f16_tile_kernel<FF, RR, PWW, PHH><<<tgrid, PWW * PHH, smem_bytes, s>>>(              \
         D11, D21, p1, p1_new, scores, H, W, radius, dil, cap_px, D21_f32);                      \

@@ -171,8 +171,12 @@ def graph_edges(cfg, seed=2):
         K = 8
         und = [(k - 1, k) for k in range(1, K)] + [(k - 3, k) for k in range(3, K)]
         return K, und
-    if cfg in ("loop64", "calib32"):
-        K, n_loop, min_gap = (64, 65, 8) if cfg == "loop64" else (32, 33, 4)
+    if cfg in ("loop64", "calib32") or cfg.startswith("loops:"):
+        if cfg.startswith("loops:"):  # "loops:K": K-1 chain edges + K+1 loop closures (E = 4K)
+            K = int(cfg.split(":")[1])
+            n_loop, min_gap = K + 1, max(2, min(8, K // 8))
+        else:
+            K, n_loop, min_gap = (64, 65, 8) if cfg == "loop64" else (32, 33, 4)
         und = [(k - 1, k) for k in range(1, K)]
         gen = torch.Generator().manual_seed(seed)
         seen = set(und)

@@ -66,6 +66,10 @@ int frodo_refine_matches_f16(const void* D11, const void* D21, const int64_t* p1
 int frodo_refine_matches_f32(const float* D11, const float* D21, const int64_t* p1,
                              int64_t* p1_new, float* max_scores, int B, int H, int W, int N, int F,
                              int radius, int dilation_max, frodo_stream_t stream);
+/* Tuning / test switch of the tile-staged fp16 kernel: query-patch edge 16 or 32, 0 = automatic
+ * (16 for F <= 24).  Both variants are bit-identical; returns the value now in force.  The
+ * environment variable FRODO_REFINE_PATCH seeds it once per process. */
+int frodo_set_refine_patch(int patch);
 
 /* ---- the matching pipeline around the two kernels ----------
  * mast3r_slam/matching.py:25-110 + mast3r_slam/image.py:5-38, which the reference runs as

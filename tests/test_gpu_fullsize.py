@@ -267,9 +267,10 @@ def test_gn_rays_odom_vs_reference(be, dev, ref_backend, capfd):
     capfd.readouterr()
 
 
-def test_refine_patch_variants_agree_bitwise(be, dev, monkeypatch):
+def test_refine_patch_variants_agree_bitwise(be, dev):
     """refine_matches runs 16x16 patches (two CTAs per SM) for F <= 24 and keeps the 32x32 kernel
-    for F = 32; both must give the same bits.  FRODO_REFINE_PATCH forces the variant."""
+    for F = 32; both must give the same bits.  frodo_set_refine_patch forces the variant."""
+    from frodo_slam_b200 import _lib
     from frodo_slam_b200 import synth
     mp = synth.MATCH_PARAMS
     B, H, W = 2, 384, 512
@@ -281,10 +282,13 @@ def test_refine_patch_variants_agree_bitwise(be, dev, monkeypatch):
     D11 = d["D11"].half().contiguous()
     D21 = d["D21"].half().reshape(B, H * W, -1).contiguous()
     out = {}
-    for v in ("16", "32"):
-        monkeypatch.setenv("FRODO_REFINE_PATCH", v)
-        pn, sc = be.refine_matches(D11, D21, p1, mp["radius"], mp["dilation_max"])
-        torch.cuda.synchronize()
-        out[v] = (pn.clone(), sc.clone())
+    try:
+        for v in ("16", "32"):
+            assert _lib.load().frodo_set_refine_patch(int(v)) == int(v)
+            pn, sc = be.refine_matches(D11, D21, p1, mp["radius"], mp["dilation_max"])
+            torch.cuda.synchronize()
+            out[v] = (pn.clone(), sc.clone())
+    finally:
+        _lib.load().frodo_set_refine_patch(0)
     assert torch.equal(out["16"][0], out["32"][0])
     assert torch.equal(out["16"][1].view(torch.int16), out["32"][1].view(torch.int16))
