@@ -468,6 +468,39 @@ def main_ours(args):
     assert int(sg.flags[1].item()) == iters and int(sg.flags[2].item()) == 0, "GN did not run clean"
     value = args.steps * iters / (ms * 1e-3)
 
+    # Parity of THIS run's code path (every N): the poses one step produces, against the
+    # single-GPU drop-in operator on the full graph, against the unmodified reference backend
+    # (oracle/_ref, gn_kernels.cu:909-995 + Eigen solve) when it is on the box, and across ranks.
+    def _rel(a, b):
+        return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-300))
+
+    step()
+    T_run = Twc.clone()
+    T_single = Twc0.clone()
+    be.gauss_newton_rays(T_single, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"],
+                         g["valid_match"], g["Q"], gp["sigma_ray"], gp["sigma_dist"], gp["C_conf"],
+                         gp["Q_conf"], gp["num_fix"], iters, 0.0)
+    parity = {"pose_rel_err_vs_single_gpu_op": _rel(T_run, T_single),
+              "pose_rel_err_vs_reference": None, "ranks_bit_identical": True, "tolerance": 1e-4}
+    if world > 1:
+        allT = [torch.empty_like(T_run) for _ in range(world)]
+        dist.all_gather(allT, T_run)
+        parity["ranks_bit_identical"] = bool(all(torch.equal(allT[0], x) for x in allT))
+    if rank == 0:
+        ref_mod = load_reference_backend()
+        if ref_mod is not None:
+            T_ref = Twc0.clone()
+            with _QuietStdout():
+                ref_mod.gauss_newton_rays(T_ref, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx_ii2jj"],
+                                          g["valid_match"], g["Q"], gp["sigma_ray"],
+                                          gp["sigma_dist"], gp["C_conf"], gp["Q_conf"],
+                                          gp["num_fix"], iters, 0.0)
+                torch.cuda.synchronize()
+            parity["pose_rel_err_vs_reference"] = _rel(T_run, T_ref)
+            parity["pose_moved_rel"] = _rel(Twc0, T_ref)  # how far the solve moved the poses
+            assert parity["pose_rel_err_vs_reference"] <= 1e-4, parity
+    assert parity["pose_rel_err_vs_single_gpu_op"] <= 1e-4 and parity["ranks_bit_identical"], parity
+
     # dominant kernel alone (accumulate, no assembly): CUDA events on the launch stream
     lib = _lib.load()
     import ctypes
@@ -646,6 +679,7 @@ def main_ours(args):
                        "edges_per_gpu": hi - lo, "sharding": f"edges/{world} + allreduce(H,g)",
                        "l2": "inputs larger than L2 (2.27 GB streamed per iteration)"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
+            "parity": parity,
             "gpu_launches": args.steps * (1 + 3 * iters),  # pack + (accumulate, assemble, solve)/iter
             "matching": matching,
             "tracking": tracking,
