@@ -64,6 +64,7 @@ SIGNATURES = {
     "frodo_match_quality": (c_int, [c_void_p] * 6 + [c_float, c_float] + [c_void_p] * 4 +
                             [c_int] * 3 + [c_void_p]),
     "frodo_gn_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "frodo_gn_chol_stamps_offset": (c_size_t, [c_int]),
     "frodo_gn_workspace_init": (c_int, [c_void_p, c_size_t, c_int, c_int, c_int, c_void_p]),
     "frodo_gn_edge_index": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                     c_void_p]),

@@ -290,9 +290,12 @@ int frodo_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fix
   double* chol = nullptr;
   if (workspace != nullptr && workspace_bytes >= gn_chol_scratch_bytes(7 * K))
     chol = static_cast<double*>(workspace);
-  return launch_gn_solve_retract(Hg, Twc, dx, K, num_fix, delta_thresh, done, info, chol,
+  const GnSystem sys = {Hg, true, nullptr, nullptr, nullptr, 0};
+  return launch_gn_solve_retract(sys, Twc, dx, K, num_fix, delta_thresh, done, info, chol, 7 * K,
                                  static_cast<cudaStream_t>(stream));
 }
+
+size_t frodo_gn_chol_stamps_offset(int K) { return gn_chol_stamps_offset(7 * (K > 0 ? K : 1)); }
 
 int frodo_gn_workspace_init(void* workspace, size_t workspace_bytes, int K, int E, int N,
                             frodo_stream_t stream) {
@@ -303,7 +306,7 @@ int frodo_gn_workspace_init(void* workspace, size_t workspace_bytes, int K, int 
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   FRODO_CUDA_TRY(cudaMemsetAsync(ws.scalars, 0, 8 * sizeof(int32_t), s));
   FRODO_CUDA_TRY(cudaMemsetAsync(ws.tickets, 0, (size_t)(E > 0 ? E : 1) * sizeof(int32_t), s));
-  return FRODO_OK;
+  return gn_chol_scratch_init(ws.chol, 7 * (K > 0 ? K : 1), s);
 }
 
 // Shared driver of the single-call Gauss-Newton entry points.  `od` (may be NULL) adds the
@@ -346,16 +349,19 @@ static int gn_run(const frodo_gn_params* params, float* Twc, const float* Xs, co
     XC = ws.packed;
   }
   for (int it = 0; it < max_iter; ++it) {
+    // the visual terms stay per-edge blocks (the solver builds its tiles from them); only the
+    // odometry terms need the dense system
     rc = frodo_gn_accumulate(params, Twc, Xs, Cs, Kmat, XC, ws.ii_row, ws.jj_row, idx_ii2jj,
-                             valid_match, Q, K, N, E, num_fix, ws.Hg, ws.edge_blocks, done,
-                             workspace, workspace_bytes, stream);
+                             valid_match, Q, K, N, E, num_fix, od != nullptr ? ws.Hg : nullptr,
+                             ws.edge_blocks, done, workspace, workspace_bytes, stream);
     if (rc) return rc;
     if (od != nullptr) {
       rc = launch_gn_add_odom(*od, Twc, K, num_fix, ws.Hg, done, odom_scratch, s);
       if (rc) return rc;
     }
-    rc = launch_gn_solve_retract(ws.Hg, Twc, dx, K, num_fix, delta_thresh, done, winfo, ws.chol,
-                                 s);
+    const GnSystem sys = {ws.Hg, od != nullptr, ws.edge_blocks, ws.ii_row, ws.jj_row, E};
+    rc = launch_gn_solve_retract(sys, Twc, dx, K, num_fix, delta_thresh, done, winfo, ws.chol,
+                                 7 * K, s);
     if (rc) return rc;
   }
   if (info != nullptr)
@@ -481,6 +487,10 @@ int frodo_gauss_newton_arena(const frodo_gn_params* params, float* Twc, const fl
   gn_carve_workspace(workspace, K_arena, E, N, &ws);
   FRODO_CUDA_TRY(cudaMemsetAsync(ws.scalars, 0, 8 * sizeof(int32_t), s));
   FRODO_CUDA_TRY(cudaMemsetAsync(ws.tickets, 0, (size_t)(E > 0 ? E : 1) * sizeof(int32_t), s));
+  {
+    const int irc = gn_chol_scratch_init(ws.chol, 7 * K_arena, s);
+    if (irc) return irc;
+  }
   int32_t* done = ws.scalars + 1;
   int32_t* winfo = ws.scalars + 2;
   const float* XC = (N % 16) == 0 ? XC_packed : nullptr;
@@ -490,16 +500,18 @@ int frodo_gauss_newton_arena(const frodo_gn_params* params, float* Twc, const fl
                                   valid_match, Q, K_arena, N, E, ws.partials, ws.tickets,
                                   ws.edge_blocks, done, s);
     if (rc) return rc;
-    rc = launch_gn_assemble(ws.edge_blocks, ii_rank, jj_rank, E, K_solve, num_fix, ws.Hg, done, s);
-    if (rc) return rc;
     if (odom != nullptr) {
+      rc = launch_gn_assemble(ws.edge_blocks, ii_rank, jj_rank, E, K_solve, num_fix, ws.Hg, done,
+                              s);
+      if (rc) return rc;
       const GnOdom od = odom_from_terms(odom);
       rc = launch_gn_add_odom_rows(od, Twc, K_solve, num_fix, ws.Hg, done, odom->odom_rank,
                                    static_cast<double*>(odom->blocks), pose_slot, s);
       if (rc) return rc;
     }
-    rc = launch_gn_solve_retract(ws.Hg, Twc, dx, K_solve, num_fix, delta_thresh, done, winfo,
-                                 ws.chol, s, pose_slot);
+    const GnSystem sys = {ws.Hg, odom != nullptr, ws.edge_blocks, ii_rank, jj_rank, E};
+    rc = launch_gn_solve_retract(sys, Twc, dx, K_solve, num_fix, delta_thresh, done, winfo,
+                                 ws.chol, 7 * K_arena, s, pose_slot);
     if (rc) return rc;
   }
   if (info != nullptr)

@@ -466,15 +466,10 @@ gn_accumulate_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
 #ifndef FRODO_ABL
 #define FRODO_ABL 0
 #endif
-#ifndef FRODO_RAYS_WS
-#define FRODO_RAYS_WS 0   // 1: warp-specialised persistent variant (gn_accumulate_ws.cuh), slower
-#endif
+// (a warp-specialised persistent variant, measured slower -- 538 vs 473 us -- is kept as an
+// experiment under profiles/experiments/gn_accumulate_ws.cuh, not in the product)
 #ifndef FRODO_RAYS_THREADS
-#if FRODO_RAYS_WS
-#define FRODO_RAYS_THREADS 512
-#else
 #define FRODO_RAYS_THREADS 128   // 4 CTAs x 128 threads per SM: 473 us; 2 x 256: 485 us; 8 x 64: 519 us
-#endif
 #endif
 constexpr int kRaysThreads = FRODO_RAYS_THREADS;        // threads per CTA of the rays kernel
 constexpr int kRaysCtasPerSM = 512 / kRaysThreads;      // 16 warps per SM either way
@@ -886,21 +881,13 @@ gn_accumulate_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
 }
 
 
-#if FRODO_RAYS_WS
-#include "gn_accumulate_ws.cuh"
-#endif
-
 }  // namespace
 
 // Points per accumulate CTA: minimises ceil(waves) * (points + fixed per-CTA cost) over a few
 // multiples of the 512-point tile (2 CTAs per SM; the fixed cost ~ 1500 points covers the
 // pipeline fill and the reduction epilogue).
 int gn_pts_per_cta(int E, int N) {
-#if FRODO_RAYS_WS
-  const long long cand[] = {2048, 4096, 8192, 12288, 16384, 24576, 32768, 49152, 65536};
-#else
   const long long cand[] = {2048, 4096, 6144, 8192, 12288, 16384, 24576, 32768};
-#endif
   const double slots = (double)kRaysCtasPerSM * kNumSMs;
   long long best = 2048;
   double best_cost = 1e300;
@@ -965,24 +952,6 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
   const bool aligned16 =
       ((reinterpret_cast<uintptr_t>(XC) | reinterpret_cast<uintptr_t>(idx) |
         reinterpret_cast<uintptr_t>(Q) | reinterpret_cast<uintptr_t>(valid)) & 15) == 0;
-#if FRODO_RAYS_WS
-  if (prm.mode == FRODO_GN_RAYS && XC != nullptr && (N % 16) == 0 && aligned16) {
-    static bool attr_set = false;
-    const size_t smem = (size_t)kWsSmemBytes;
-    if (!attr_set) {
-      FRODO_CUDA_TRY(cudaFuncSetAttribute(gn_accumulate_rays_ws_kernel,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr_set = true;
-    }
-    const int nitems = nchunks * E;
-    gn_accumulate_rays_ws_kernel<<<nitems < kNumSMs ? nitems : kNumSMs, kWsThreads, smem, s>>>(
-        prm, Twc, reinterpret_cast<const float4*>(XC),
-        reinterpret_cast<const float4*>(XC) + (size_t)K * N, ii_row, jj_row, idx, valid, Q, N, ppc,
-        nchunks, nitems, partials, tickets, edge_blocks, done);
-    FRODO_CUDA_TRY(cudaGetLastError());
-    return FRODO_OK;
-  }
-#else
   // packed fast path (all three modes): needs the repacked pointmaps and 16-byte alignment;
   // calib additionally needs N < 2^32 target pixels, which N as an int guarantees
   if (XC != nullptr && (N % 16) == 0 && aligned16 &&
@@ -1016,7 +985,6 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
     FRODO_CUDA_TRY(cudaGetLastError());
     return FRODO_OK;
   }
-#endif
   switch (prm.mode) {
     case FRODO_GN_RAYS:
       gn_accumulate_kernel<FRODO_GN_RAYS><<<grid, kThreads, 0, s>>>(

@@ -17,7 +17,7 @@ struct GnWorkspace {
   float* partials;     // [E * nchunks * 35]
   double* edge_blocks; // [E * 35]
   double* Hg;          // [(n+1) * n]
-  double* chol;        // tile scratch of the cluster Cholesky (gn_chol_scratch_bytes)
+  double* chol;        // scratch of the dataflow Cholesky (gn_chol_scratch_bytes)
   float* packed;       // [2 * K * N * 4]: XC float4 (x,y,z,c) then XP pair-interleaved
   size_t packed_off;   // byte offset of `packed` inside the workspace
   size_t bytes;
@@ -64,12 +64,28 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
                          double* edge_blocks, const int32_t* done, cudaStream_t s);
 int launch_gn_assemble(const double* edge_blocks, const int32_t* ii_row, const int32_t* jj_row,
                        int E, int K, int num_fix, double* Hg, const int32_t* done, cudaStream_t s);
-int launch_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fix,
+// Where the normal equations of one iteration are: the dense fp64 [H | g] (`Hg`, valid when
+// `dense` is set) or the per-edge blocks the accumulate kernel left (`edge_blocks` + the edge
+// ranks).  `Hg` must always point at an [(n+1) x n] buffer: paths that need the dense form build
+// it there.
+struct GnSystem {
+  double* Hg;
+  bool dense;
+  const double* edge_blocks;
+  const int32_t* ii_row;
+  const int32_t* jj_row;
+  int E;
+};
+// n_max: the system size the Cholesky scratch was laid out and initialised for (7 x keyframes).
+int launch_gn_solve_retract(const GnSystem& sys, float* Twc, float* dx, int K, int num_fix,
                             float delta_thresh, int32_t* done, int32_t* info, double* chol_scratch,
-                            cudaStream_t s, const int32_t* pose_rows = nullptr);
+                            int n_max, cudaStream_t s, const int32_t* pose_rows = nullptr);
 size_t gn_chol_scratch_bytes(int n);
-int launch_chol_cluster(double* Hg, float* Twc, float* dx, int K, int num_fix, float delta_thresh,
-                        int32_t* done, int32_t* info, double* chol_scratch, int* handled,
-                        cudaStream_t s, const int32_t* pose_rows = nullptr);
+size_t gn_chol_stamps_offset(int n);
+int gn_chol_scratch_init(double* scratch, int n_max, cudaStream_t s);
+int launch_chol_flow(const double* Hg, const double* edge_blocks, const int32_t* ii_row,
+                     const int32_t* jj_row, int E, float* Twc, float* dx, int K, int num_fix,
+                     float delta_thresh, int32_t* done, int32_t* info, double* chol_scratch,
+                     int n_max, int* handled, cudaStream_t s, const int32_t* pose_rows = nullptr);
 
 }  // namespace frodo

@@ -205,8 +205,8 @@ solve_retract_kernel(double* __restrict__ A, float* __restrict__ Twc, float* __r
 
 // ---------------------------------------------------------------------------------------
 // Small systems (n <= 63: up to 9 free keyframes, i.e. the sliding-window local optimisation of
-// the fork's tracker, tracker.py:27-60): the cluster machinery of gn_chol_cluster.cu (cluster
-// barriers, L2 scratch, bulk copies) costs ~50 us for two 32x32 tiles.  Here the whole
+// the fork's tracker, tracker.py:27-60): the multi-CTA machinery of gn_chol_flow.cu (cooperative
+// launch, L2 tile array, flags) is pointless for two 32x32 tiles.  Here the whole
 // (n+1) x n system [H ; g^T] sits in the shared memory of one CTA (row pitch 65 doubles:
 // column accesses are conflict-free) and a right-looking factorisation runs with two block
 // barriers per pivot: every thread forms 1/sqrt(a_jj) redundantly, 64 threads scale column j,
@@ -284,23 +284,35 @@ solve_small_kernel(const double* __restrict__ A, float* __restrict__ Twc, float*
 
 }  // namespace
 
-int launch_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fix,
+int launch_gn_solve_retract(const GnSystem& sys, float* Twc, float* dx, int K, int num_fix,
                             float delta_thresh, int32_t* done, int32_t* info, double* chol_scratch,
-                            cudaStream_t s, const int32_t* pose_rows) {
+                            int n_max, cudaStream_t s, const int32_t* pose_rows) {
   const int n = 7 * (K - num_fix);
   if (n <= 0) return FRODO_OK;
-  if (n <= kSmallN) {  // sliding-window sized systems: register-resident single-CTA solve
+  double* Hg = sys.Hg;
+  auto need_dense = [&]() -> int {
+    if (sys.dense) return FRODO_OK;
+    return launch_gn_assemble(sys.edge_blocks, sys.ii_row, sys.jj_row, sys.E, K, num_fix, Hg, done,
+                              s);
+  };
+  if (n <= kSmallN) {  // sliding-window sized systems: one CTA, system in shared memory
+    const int rc = need_dense();
+    if (rc != FRODO_OK) return rc;
     solve_small_kernel<<<1, kSmallThreads, 0, s>>>(Hg, Twc, dx, n, K, num_fix, delta_thresh, done,
                                                    info, pose_rows);
     FRODO_CUDA_TRY(cudaGetLastError());
     return FRODO_OK;
   }
-  // fast path: cluster-resident tiled Cholesky (gn_chol_cluster.cu)
+  // fast path: dataflow tiled Cholesky over the whole GPU (gn_chol_flow.cu), tiles built from
+  // the dense system or straight from the per-edge blocks
   int handled = 0;
-  const int rc = launch_chol_cluster(Hg, Twc, dx, K, num_fix, delta_thresh, done, info,
-                                     chol_scratch, &handled, s, pose_rows);
+  int rc = launch_chol_flow(sys.dense ? Hg : nullptr, sys.edge_blocks, sys.ii_row, sys.jj_row,
+                            sys.E, Twc, dx, K, num_fix, delta_thresh, done, info, chol_scratch,
+                            n_max, &handled, s, pose_rows);
   if (rc != FRODO_OK || handled) return rc;
-  // fallback for systems that do not fit the cluster's shared memory
+  // fallback: no cooperative launch on this device, no scratch, or beyond the tile plan
+  rc = need_dense();
+  if (rc != FRODO_OK) return rc;
   static PerDeviceOnce once;
   int dev;
   if (once.needed(&dev)) {

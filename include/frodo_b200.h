@@ -155,10 +155,15 @@ typedef struct frodo_gn_params {
  * keyframes, E (local) directed edges and N points per keyframe. */
 size_t frodo_gn_workspace_bytes(int K, int E, int N);
 
-/* Zeroes the control words (tickets, convergence flag, counters) of a workspace;
- * call once before the first frodo_gn_accumulate on a fresh or reused buffer. */
+/* Zeroes the control words (tickets, convergence flag, counters, the ready flags of the
+ * multi-CTA Cholesky) of a workspace; call once per solve before the first
+ * frodo_gn_accumulate / frodo_gn_solve_retract on a fresh or reused buffer. */
 int frodo_gn_workspace_init(void* workspace, size_t workspace_bytes, int K, int E, int N,
                             frodo_stream_t stream);
+/* Profiling aid: byte offset (inside a workspace laid out for K keyframes) of the clock64
+ * phase stamps the Cholesky's spine CTA writes when the environment has FRODO_CHOL_STAMPS=1
+ * (profiles/chol_phases.py). */
+size_t frodo_gn_chol_stamps_offset(int K);
 
 /* Rays fast path: repacks the keyframe pointmaps Xs [K,N,3] and confidences Cs [K,N] into
  * XC, a 16-byte aligned region of frodo_gn_packed_bytes(K, N) bytes: first [K,N] float4
@@ -206,7 +211,10 @@ int frodo_gn_accumulate(const frodo_gn_params* params, const float* Twc, const f
  * k >= num_fix (pose_retr_kernel :522-560); if ||dx||_2 < delta_thresh sets
  * *done = 1 (:986-989).  Hg is destroyed.  Skipped when *done != 0 on entry.
  * info (device int32[2], may be NULL): [0] += 1 per executed iteration,
- * [1] += 1 per failed factorisation. */
+ * [1] += 1 per failed factorisation.
+ * workspace: a buffer of frodo_gn_workspace_bytes(K, E, N) bytes prepared by
+ * frodo_gn_workspace_init (the multi-CTA factorisation keeps its tile array and ready flags
+ * at its start); NULL or too small selects a single-CTA factorisation. */
 int frodo_gn_solve_retract(double* Hg, float* Twc, float* dx, int K, int num_fix,
                            float delta_thresh, int32_t* done, int32_t* info, void* workspace,
                            size_t workspace_bytes, frodo_stream_t stream);

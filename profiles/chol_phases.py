@@ -1,13 +1,16 @@
 #!/usr/bin/env python
-"""Phase profile of the cluster Cholesky (chol_cluster_kernel): reads the clock64 stamps
-CTA 0 leaves behind the tile scratch (gn_solve.cu, `stamps`) after one GN iteration and
-prints the time spent per phase (panel / trailing update incl. look-ahead diagonal per
-tile column, then the back substitution).
-Usage: python profiles/chol_phases.py [--kf loop64] [--hw 384x512]"""
+"""Phase profile of the dataflow Cholesky (chol_flow_kernel, csrc/gn_chol_flow.cu): reads the
+clock64 stamps the spine CTA leaves in the workspace (FRODO_CHOL_STAMPS=1) after one GN
+iteration and prints the time per phase: per tile column the diagonal factor + inversion, the
+sub-diagonal panel product + publication, the update of the next diagonal tile; then the back
+substitution and the pose update.  Also times the kernel with CUDA events.
+Usage: FRODO_CHOL_STAMPS=1 python profiles/chol_phases.py [--kf loop64] [--hw 96x128]"""
 import argparse
+import ctypes
 import os
 import sys
 
+os.environ.setdefault("FRODO_CHOL_STAMPS", "1")
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch  # noqa: E402
@@ -18,8 +21,10 @@ ap.add_argument("--hw", default="96x128")
 args = ap.parse_args()
 H, W = (int(x) for x in args.hw.split("x"))
 
-from frodo_slam_b200 import backends, dist as fdist, synth  # noqa: E402
+from frodo_slam_b200 import _lib, backends, synth  # noqa: E402
+from frodo_slam_b200.backends import _ptr, _stream  # noqa: E402
 
+lib = _lib.load()
 dev = torch.device("cuda:0")
 gp = synth.GN_PARAMS
 K, und = synth.graph_edges(args.kf)
@@ -27,42 +32,70 @@ g = synth.keyframe_graph(K, H, W, und, seed=1, device=dev)
 E, N = g["ii"].shape[0], H * W
 prm = backends.make_params("rays", sigma_ray=gp["sigma_ray"], sigma_dist=gp["sigma_dist"],
                            C_thresh=gp["C_conf"], Q_thresh=gp["Q_conf"])
-Twc = g["Twc"].clone()
-sg = fdist.ShardedGaussNewton(prm, Twc, g["Xs"], g["Cs"], None, g["ii"], g["jj"],
-                              g["idx_ii2jj"].view(E, N), g["valid_match"].view(E, N),
-                              g["Q"].view(E, N), 0, E, 1)
 n = 7 * (K - 1)
 T, Tc = (n + 1 + 31) // 32, (n + 31) // 32
-off = (T * (T + 1) // 2 * 1024 + 32) * 8
-sg.ws[off:off + 128 * 8].zero_()
-for _ in range(3):
+nbytes = lib.frodo_gn_workspace_bytes(K, E, N)
+ws = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+st_off = lib.frodo_gn_chol_stamps_offset(K)
+Hg = torch.empty((n + 1) * n, dtype=torch.float64, device=dev)
+eb = torch.empty((E, 35), dtype=torch.float64, device=dev)
+ii_row = torch.empty(E, dtype=torch.int32, device=dev)
+jj_row = torch.empty(E, dtype=torch.int32, device=dev)
+dx = torch.zeros(K - 1, 7, device=dev)
+s = _stream()
+_lib.check(lib.frodo_gn_workspace_init(_ptr(ws), nbytes, K, E, N, s))
+_lib.check(lib.frodo_gn_edge_index(_ptr(g["ii"]), _ptr(g["jj"]), E, _ptr(ii_row), _ptr(jj_row), None, s))
+Twc = g["Twc"].clone()
+
+
+def system():
+    _lib.check(lib.frodo_gn_accumulate(
+        ctypes.byref(prm), _ptr(Twc), _ptr(g["Xs"]), _ptr(g["Cs"]), None, None, _ptr(ii_row),
+        _ptr(jj_row), _ptr(g["idx_ii2jj"]), _ptr(g["valid_match"]), _ptr(g["Q"]), K, N, E, 1,
+        _ptr(Hg), _ptr(eb), None, _ptr(ws), nbytes, s))
+
+
+def solve():
+    _lib.check(lib.frodo_gn_solve_retract(_ptr(Hg), _ptr(Twc), _ptr(dx), K, 1, 0.0, None, None,
+                                          _ptr(ws), nbytes, s))
+
+
+times = []
+for it in range(6):
     Twc.copy_(g["Twc"])
-    sg.solve(1, 0.0)
-torch.cuda.synchronize()
-st = sg.ws[off:off + 128 * 8].view(torch.int64).cpu().numpy().astype("float64")
+    system()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    solve()
+    e1.record()
+    torch.cuda.synchronize()
+    times.append(e0.elapsed_time(e1) * 1e3)
+st = ws[st_off:st_off + 1024 * 8].view(torch.int64).cpu().numpy().astype("float64")
 mhz = 1965.0
 us = lambda a, b: (b - a) / mhz  # noqa: E731
-print(f"n={n} T={T} Tc={Tc}  (clock64 cycles at {mhz:.0f} MHz -> us)")
-print(f"load tiles + first diagonal {us(st[0], st[1]):8.2f} us")
-tot = {"panel": 0.0, "update": 0.0, "barrier_x": 0.0}
+print(f"n={n} T={T} Tc={Tc}; kernel by CUDA events (us): " + " ".join(f"{t:.1f}" for t in times))
+print(f"(clock64 cycles of the spine CTA at {mhz:.0f} MHz -> us; dense-Hg tile build)")
+print(f"wait for + load the first diagonal tile {us(st[0], st[1]):8.2f} us")
+tot = {"factor+invert": 0.0, "panel+publish": 0.0, "diag update": 0.0}
 for k in range(Tc):
-    a, b, c = st[2 + 3 * k], st[3 + 3 * k], st[4 + 3 * k]
-    nxt = st[2 + 3 * (k + 1)] if k + 1 < Tc else st[2 + 3 * Tc]
-    tot["panel"] += us(a, b)
-    tot["update"] += us(b, c)
-    tot["barrier_x"] += us(c, nxt)
-    print(f"col {k:2d}: panel(+Y) {us(a, b):7.2f}  update(+look-ahead diag) {us(b, c):7.2f}  "
-          f"barrier X {us(c, nxt):6.2f}")
+    a, b, c, d = (st[2 + 4 * k + i] for i in range(4))
+    c = c if c > 0 else b
+    tot["factor+invert"] += us(a, b)
+    tot["panel+publish"] += us(b, c)
+    tot["diag update"] += us(c, d)
+    print(f"col {k:2d}: factor+invert (+fetch) {us(a, b):6.2f}  panel+publish {us(b, c):6.2f}  "
+          f"diag update {us(c, d):6.2f}")
 print({k: round(float(v), 2) for k, v in tot.items()})
-print(f"back substitution   {us(st[2 + 3 * Tc], st[3 + 3 * Tc]):8.2f} us")
-print(f"total               {us(st[0], st[3 + 3 * Tc]):8.2f} us")
-if st[116] > 0:
-    print(f"pose update (dx, retraction)  {us(st[3 + 3 * Tc], st[116]):8.2f} us")
-    wall = (st[119] - st[118]) / 1e3
-    print(f"wall clock (globaltimer) start -> end of kernel body {wall:8.2f} us  => SM clock "
-          f"{(st[116] - st[0]) / wall:7.1f} MHz during the kernel")
-# cycles accumulated by every diagonal-tile call since the workspace was allocated (3 solves)
-if st[120] > 0:
-    calls = 3 * Tc
-    print(f"diagonal tile: factor {st[120] / mhz / calls:6.2f} us, inverse W {st[121] / mhz / calls:6.2f} us "
-          f"per tile (mean of {calls} calls)")
+print("background of column k, relative to the start of its factor phase (us): G flag seen | "
+      "all tiles copied | helpers done | phase end")
+for k in range(1, Tc - 1):
+    b0 = st[256 + 8 * k]
+    print(f"col {k:2d}: " + " | ".join(f"{us(b0, st[256 + 8 * k + i]):5.2f}" for i in (2, 3, 4))
+          + f" | {us(st[2 + 4 * k], st[3 + 4 * k]) + us(st[3 + 4 * k], st[4 + 4 * k]):5.2f} (warp-1 view); "
+          f"L product alone {us(st[3 + 4 * k], st[256 + 8 * k + 5]):5.2f}")
+f_end, b_end, end = st[2 + 4 * Tc], st[3 + 4 * Tc], st[4 + 4 * Tc]
+print(f"factorisation total {us(st[0], f_end):8.2f} us")
+print(f"back substitution   {us(f_end, b_end):8.2f} us  (flag sweep {us(f_end, st[100]):.2f}; columns "
+      + " ".join(f"{us(st[101 + k + 1] if k + 1 < Tc else st[100], st[101 + k]):.2f}" for k in range(Tc - 1, -1, -1)) + ")")
+print(f"pose update         {us(b_end, end):8.2f} us")
+print(f"spine total         {us(st[0], end):8.2f} us")
