@@ -86,13 +86,9 @@ for k in range(Tc):
     print(f"col {k:2d}: factor+invert (+fetch) {us(a, b):6.2f}  panel+publish {us(b, c):6.2f}  "
           f"diag update {us(c, d):6.2f}")
 print({k: round(float(v), 2) for k, v in tot.items()})
-print("background of column k, relative to the start of its factor phase (us): G flag seen | "
-      "all tiles copied | helpers done | phase end")
-for k in range(1, Tc - 1):
-    b0 = st[256 + 8 * k]
-    print(f"col {k:2d}: " + " | ".join(f"{us(b0, st[256 + 8 * k + i]):5.2f}" for i in (2, 3, 4))
-          + f" | {us(st[2 + 4 * k], st[3 + 4 * k]) + us(st[3 + 4 * k], st[4 + 4 * k]):5.2f} (warp-1 view); "
-          f"L product alone {us(st[3 + 4 * k], st[256 + 8 * k + 5]):5.2f}")
+print("warp 0: factor start -> end (us) / start-to-start period:")
+print(" ".join(f"{us(st[768 + 2 * k], st[768 + 2 * k + 1]):.2f}/{us(st[768 + 2 * k], st[768 + 2 * k + 2]) if k + 1 < Tc else 0:.2f}"
+               for k in range(Tc)))
 f_end, b_end, end = st[2 + 4 * Tc], st[3 + 4 * Tc], st[4 + 4 * Tc]
 print(f"factorisation total {us(st[0], f_end):8.2f} us")
 print(f"back substitution   {us(f_end, b_end):8.2f} us  (flag sweep {us(f_end, st[100]):.2f}; columns "
