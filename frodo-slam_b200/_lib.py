@@ -93,6 +93,9 @@ SIGNATURES = {
     "frodo_gn_peer_allreduce": (c_int, [c_void_p, c_void_p, c_size_t, c_int, c_int, c_int,
                                         ctypes.c_uint32, c_void_p, c_size_t, c_void_p, c_void_p]),
     "frodo_track_workspace_bytes": (c_size_t, [c_int]),
+    "frodo_track_pose_static_max_points": (c_int, []),
+    "frodo_track_pose_static": (c_int, [ctypes.POINTER(TrackParams)] + [c_void_p] * 10 + [c_int] +
+                                [c_void_p] * 5),
     "frodo_track_pose": (c_int, [ctypes.POINTER(TrackParams)] + [c_void_p] * 10 + [c_int] +
                          [c_void_p] * 5 + [c_size_t, c_void_p]),
 }

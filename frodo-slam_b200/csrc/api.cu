@@ -575,4 +575,31 @@ int frodo_track_pose(const frodo_track_params* params, const float* Xf, const in
                            static_cast<cudaStream_t>(stream));
 }
 
+int frodo_track_pose_static_max_points(void) { return track_static_max_points(); }
+
+int frodo_track_pose_static(const frodo_track_params* params, const float* Xf,
+                            const int64_t* idx_f2k, const float* Xk, const float* Qk,
+                            const uint8_t* valid, const float* meas_k,
+                            const uint8_t* valid_meas_k, const float* Kmat, const float* T_WCf,
+                            const float* T_WCk, int N, float* T_WCf_new, float* T_CkCf,
+                            int32_t* info, double* costs, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(params != nullptr);
+  FRODO_ARG_CHECK(params->mode == FRODO_GN_RAYS || params->mode == FRODO_GN_CALIB);
+  FRODO_ARG_CHECK(params->sigma_a > 0.0f && params->sigma_b > 0.0f && params->huber > 0.0f);
+  FRODO_ARG_CHECK(params->max_iters >= 0 && N >= 0);
+  FRODO_ARG_CHECK(T_WCf && T_WCk && T_WCf_new && T_CkCf);
+  FRODO_ARG_CHECK(N == 0 || (Xf && Qk && valid));
+  if (params->mode == FRODO_GN_RAYS) {
+    FRODO_ARG_CHECK(N == 0 || Xk != nullptr);
+  } else {
+    FRODO_ARG_CHECK(Kmat != nullptr);
+    FRODO_ARG_CHECK(N == 0 || (params->raw_calib ? Xk != nullptr : (meas_k && valid_meas_k)));
+    FRODO_ARG_CHECK(params->height > 0 && params->width > 0);
+    FRODO_ARG_CHECK(!params->raw_calib || (long long)params->height * params->width == N);
+  }
+  return launch_track_pose_static(*params, Xf, idx_f2k, Xk, Qk, valid, meas_k, valid_meas_k, Kmat,
+                                  T_WCf, T_WCk, N, T_WCf_new, T_CkCf, info, costs,
+                                  static_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

@@ -96,4 +96,11 @@ int launch_track_pose(const frodo_track_params& prm, const float* Xf, const int6
                       const float* T_WCk, int N, float* T_WCf_out, float* T_CkCf_out,
                       int32_t* info, double* costs, void* workspace, cudaStream_t s);
 
+int track_static_max_points();
+int launch_track_pose_static(const frodo_track_params& prm, const float* Xf, const int64_t* idx,
+                             const float* Xk, const float* Qk, const uint8_t* valid,
+                             const float* meas, const uint8_t* valid_meas, const float* Kmat,
+                             const float* T_WCf, const float* T_WCk, int N, float* T_WCf_out,
+                             float* T_CkCf_out, int32_t* info, double* costs, cudaStream_t s);
+
 }  // namespace frodo

@@ -540,4 +540,57 @@ int launch_track_pose(const frodo_track_params& prm, const float* Xf, const int6
   return FRODO_OK;
 }
 
+// ---------------------------------------------------------------------------------------
+// Allocation-free variant (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA graph capture, tight serving loops).  The
+// workspace of the solve above lives in a file-scope device array sized for frames of up to
+// kStaticMaxPoints points; every GPU that loads the library holds these bytes until exit.
+// All calls on a device share the array: the grid-barrier words are cleared by every call
+// (launch_track_pose does that with a stream-ordered memset) and the rest is written before it
+// is read, so stale contents of the previous call are harmless -- but two calls that overlap
+// on the GPU (different streams) race on it.
+namespace {
+constexpr int kStaticMaxPoints = 512 * 384;  // one 512x384 frame (BASELINE.json's size)
+constexpr size_t static_up(size_t x) { return (x + 255) / 256 * 256; }
+// the same layout track_carve() produces for N = kStaticMaxPoints (checked at set-up)
+constexpr size_t kStaticBytes = static_up(64) +
+                                static_up((size_t)2 * kGridMax * kSums * sizeof(double)) +
+                                static_up((size_t)kRec * kStaticMaxPoints * sizeof(float));
+static __device__ __align__(256) unsigned char g_track_scratch[kStaticBytes];
+}  // namespace
+
+int track_static_max_points() { return kStaticMaxPoints; }
+
+int launch_track_pose_static(const frodo_track_params& prm, const float* Xf, const int64_t* idx,
+                             const float* Xk, const float* Qk, const uint8_t* valid,
+                             const float* meas, const uint8_t* valid_meas, const float* Kmat,
+                             const float* T_WCf, const float* T_WCk, int N, float* T_WCf_out,
+                             float* T_CkCf_out, int32_t* info, double* costs, cudaStream_t s) {
+  if (N > kStaticMaxPoints || track_workspace_bytes(N) > kStaticBytes) {
+    set_error("frodo_track_pose_static: N = %d exceeds the built-in scratch (at most %d points); "
+              "use frodo_track_pose with a caller-provided workspace", N, kStaticMaxPoints);
+    return FRODO_ERR_ARG;
+  }
+  // In host code `g_track_scratch` is only a handle for the symbol, not a device address:
+  // resolve it once per device, with that device current.
+  static void* dev_ptr[kMaxDevices] = {};
+  int dev = -1;
+  FRODO_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) {
+    set_error("frodo_track_pose_static: device ordinal %d not supported", dev);
+    return FRODO_ERR_ARG;
+  }
+  if (dev_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    FRODO_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_track_scratch));
+    if (ptr == nullptr || (reinterpret_cast<uintptr_t>(ptr) & 255u) != 0) {
+      set_error("frodo_track_pose_static: could not resolve the scratch symbol");
+      return FRODO_ERR_CUDA;
+    }
+    dev_ptr[dev] = ptr;
+  }
+  return launch_track_pose(prm, Xf, idx, Xk, Qk, valid, meas, valid_meas, Kmat, T_WCf, T_WCk, N,
+                           T_WCf_out, T_CkCf_out, info, costs, dev_ptr[dev], s);
+}
+
 }  // namespace frodo

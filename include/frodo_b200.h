@@ -373,6 +373,27 @@ int frodo_track_pose(const frodo_track_params* params, const float* Xf, const in
                      double* costs, void* workspace, size_t workspace_bytes,
                      frodo_stream_t stream);
 
+/* frodo_track_pose without a workspace argument and without any allocation.  NO COUNTERPART IN
+ * THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The scratch of the solve (grid-barrier words, per-CTA partial sums, the overflow record
+ * buffer) lives in a static device array inside the library, sized for
+ * frodo_track_pose_static_max_points() = 196,608 points (one 512x384 frame), 6.9 MB held by
+ * every GPU that loads the library until the process exits.  N beyond that limit is rejected
+ * with FRODO_ERR_ARG (use frodo_track_pose with your own workspace).  The call launches the same
+ * kernel and calls no cudaMalloc / cudaFree / allocating library routine; inputs and outputs
+ * are the caller's, exactly as for frodo_track_pose, and the results are bit-identical to it.
+ * Every call on a device shares the one array: what must start at zero is cleared by each call
+ * (stream-ordered), so back-to-back calls on one stream are safe, but calls that OVERLAP on the
+ * GPU (different streams) race on it -- serialise them or use frodo_track_pose. */
+int frodo_track_pose_static_max_points(void);
+int frodo_track_pose_static(const frodo_track_params* params, const float* Xf,
+                            const int64_t* idx_f2k, const float* Xk, const float* Qk,
+                            const uint8_t* valid, const float* meas_k,
+                            const uint8_t* valid_meas_k, const float* Kmat, const float* T_WCf,
+                            const float* T_WCk, int N, float* T_WCf_new, float* T_CkCf,
+                            int32_t* info, double* costs, frodo_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
