@@ -36,6 +36,13 @@ class TrackParams(ctypes.Structure):
                 ("raw_calib", c_int)]
 
 
+class GnPeer(ctypes.Structure):
+    """struct frodo_gn_peer (include/frodo_b200.h)."""
+    _fields_ = [("peer_buffers", c_void_p), ("local_buffer", c_void_p), ("world", c_int),
+                ("rank", c_int), ("max_edges", c_int), ("epoch0", ctypes.c_uint32),
+                ("arrivals0", ctypes.c_uint32 * 2)]
+
+
 class OdomTerms(ctypes.Structure):
     """struct frodo_gn_odom_terms (include/frodo_b200.h)."""
     _fields_ = [("odom_ii_row", c_void_p), ("odom_jj_row", c_void_p), ("odom_rank", c_void_p),
@@ -90,6 +97,11 @@ SIGNATURES = {
     "frodo_gn_odom_blocks_bytes": (c_size_t, [c_int]),
     "frodo_gn_add_odom": (c_int, [ctypes.POINTER(OdomTerms), c_void_p, c_void_p, c_int, c_int,
                                   c_void_p, c_void_p, c_void_p]),
+    "frodo_gn_peer_buffer_bytes": (c_size_t, [c_int]),
+    "frodo_gauss_newton_sharded": (c_int, [ctypes.POINTER(GnParams)] + [c_void_p] * 6 +
+                                   [c_int] * 3 + [c_void_p] * 3 + [c_int] * 4 + [c_float] +
+                                   [ctypes.POINTER(GnPeer), ctypes.POINTER(OdomTerms)] +
+                                   [c_void_p] * 4 + [c_size_t, c_void_p]),
     "frodo_gn_peer_allreduce": (c_int, [c_void_p, c_void_p, c_size_t, c_int, c_int, c_int,
                                         ctypes.c_uint32, c_void_p, c_size_t, c_void_p, c_void_p]),
     "frodo_track_workspace_bytes": (c_size_t, [c_int]),

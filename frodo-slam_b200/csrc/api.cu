@@ -519,6 +519,102 @@ int frodo_gauss_newton_arena(const frodo_gn_params* params, float* Twc, const fl
   return FRODO_OK;
 }
 
+/* ---- edge-sharded multi-GPU driver: the whole solve in one call -------------- */
+size_t frodo_gn_peer_buffer_bytes(int max_edges) {
+  return (size_t)2 * (size_t)(max_edges > 0 ? max_edges : 1) * kGnBlock * sizeof(double) + 256;
+}
+
+int frodo_gauss_newton_sharded(const frodo_gn_params* params, float* Twc, const float* Xs,
+                               const float* Cs, const float* Kmat, const int32_t* ii_row,
+                               const int32_t* jj_row, int E, int edge_lo, int edge_hi,
+                               const int64_t* idx_local, const uint8_t* valid_local,
+                               const float* Q_local, int K, int N, int num_fix, int max_iter,
+                               float delta_thresh, const frodo_gn_peer* peer,
+                               const frodo_gn_odom_terms* odom, float* dx, int32_t* done,
+                               int32_t* info, void* workspace, size_t workspace_bytes,
+                               frodo_stream_t stream) {
+  FRODO_ARG_CHECK(params != nullptr && K >= 1 && N >= 0 && E >= 0 && num_fix >= 0 && num_fix <= K);
+  FRODO_ARG_CHECK(edge_lo >= 0 && edge_lo <= edge_hi && edge_hi <= E && E <= 65535);
+  FRODO_ARG_CHECK(params->mode != FRODO_GN_CALIB || Kmat != nullptr);
+  const int El = edge_hi - edge_lo;
+  FRODO_ARG_CHECK(workspace != nullptr && done != nullptr);
+  FRODO_ARG_CHECK(workspace_bytes >= gn_carve_workspace(nullptr, K, E > 0 ? E : 1, N, nullptr));
+  FRODO_ARG_CHECK(Twc && (K == num_fix || dx));
+  FRODO_ARG_CHECK(E == 0 || (Xs && Cs && ii_row && jj_row));
+  FRODO_ARG_CHECK(El == 0 || (idx_local && valid_local && Q_local));
+  const bool multi = peer != nullptr && peer->world > 1;
+  if (multi) {
+    FRODO_ARG_CHECK(peer->world <= 16 && peer->rank >= 0 && peer->rank < peer->world);
+    FRODO_ARG_CHECK(peer->peer_buffers != nullptr && peer->local_buffer != nullptr);
+    FRODO_ARG_CHECK(peer->max_edges >= E);
+  }
+  if (odom != nullptr) {
+    FRODO_ARG_CHECK(params->mode == FRODO_GN_RAYS);
+    const int orc = check_odom_terms(odom);
+    if (orc) return orc;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  GnWorkspace ws;
+  gn_carve_workspace(workspace, K, E > 0 ? E : 1, N, &ws);  // sized for all E edges
+  int rc = frodo_gn_workspace_init(workspace, workspace_bytes, K, E > 0 ? E : 1, N, stream);
+  if (rc) return rc;
+  const float* XC = nullptr;
+  if (El > 0 && N > 0 && (N % 16) == 0 && max_iter > 0) {
+    rc = launch_gn_pack_points(Xs, Cs, K, N, ws.packed, s);
+    if (rc) return rc;
+    XC = ws.packed;
+  }
+  // layout of a rank's exchange buffer: [blocks of even epochs | blocks of odd epochs | counters]
+  const size_t eb_bytes = multi ? (size_t)peer->max_edges * kGnBlock * sizeof(double) : 0;
+  uint32_t arrivals[2] = {multi ? peer->arrivals0[0] : 0u, multi ? peer->arrivals0[1] : 0u};
+  for (int it = 0; it < max_iter; ++it) {
+    const double* eb_all = ws.edge_blocks;
+    const uint32_t* wait_counter = nullptr;
+    uint32_t wait_target = 0;
+    GnPeerOut po = {};
+    if (multi) {
+      const uint32_t epoch = peer->epoch0 + (uint32_t)it + 1u;
+      const int par = (int)(epoch & 1u);
+      po.bufs = static_cast<void* const*>(peer->peer_buffers);
+      po.eb_offset = (size_t)par * eb_bytes;
+      po.cnt_offset = 2 * eb_bytes + (size_t)par * 128;
+      po.world = peer->world;
+      po.edge_base = edge_lo;
+      char* local = static_cast<char*>(peer->local_buffer);
+      eb_all = reinterpret_cast<const double*>(local + po.eb_offset);
+      wait_counter = reinterpret_cast<const uint32_t*>(local + po.cnt_offset);
+      arrivals[par] += (uint32_t)E;  // every epoch brings E arrivals, on every rank
+      wait_target = arrivals[par];
+    }
+    rc = launch_gn_accumulate(*params, Twc, Xs, Cs, Kmat, XC, ii_row + edge_lo, jj_row + edge_lo,
+                              idx_local, valid_local, Q_local, K, N, El, ws.partials, ws.tickets,
+                              ws.edge_blocks + (size_t)edge_lo * kGnBlock, done, s,
+                              multi ? &po : nullptr);
+    if (rc) return rc;
+    GnSystem sys = {ws.Hg, false, eb_all, ii_row, jj_row, E};
+    sys.wait_counter = wait_counter;
+    sys.wait_target = wait_target;
+    if (odom != nullptr) {  // the odometry terms need the dense system (replicated, O(K) work)
+      if (wait_counter != nullptr) {
+        rc = launch_gn_peer_wait(wait_counter, wait_target, done, info, s);
+        if (rc) return rc;
+      }
+      rc = launch_gn_assemble(eb_all, ii_row, jj_row, E, K, num_fix, ws.Hg, done, s);
+      if (rc) return rc;
+      const GnOdom od = odom_from_terms(odom);
+      rc = launch_gn_add_odom_rows(od, Twc, K, num_fix, ws.Hg, done, odom->odom_rank,
+                                   static_cast<double*>(odom->blocks), nullptr, s);
+      if (rc) return rc;
+      sys.dense = true;
+      sys.wait_counter = nullptr;
+    }
+    rc = launch_gn_solve_retract(sys, Twc, dx, K, num_fix, delta_thresh, done, info, ws.chol,
+                                 7 * K, s);
+    if (rc) return rc;
+  }
+  return FRODO_OK;
+}
+
 int frodo_gn_peer_allreduce(const void* peer_buffers, const void* peer_signal_pads,
                             size_t buffer_offset_bytes, int signal_slot0, int rank, int world,
                             uint32_t epoch, double* out, size_t n, const int32_t* done,

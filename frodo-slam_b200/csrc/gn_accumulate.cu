@@ -253,12 +253,24 @@ __device__ __forceinline__ void epi_sync() {
   else ptx::named_bar_sync<BAR, THREADS>();
 }
 
+// One arrival of this rank on rank r's counter (release: ordered after this CTA's block stores).
+__device__ __forceinline__ void peer_arrive(const GnPeerOut& peer, int r) {
+  uint32_t* cnt = reinterpret_cast<uint32_t*>(static_cast<char*>(peer.bufs[r]) + peer.cnt_offset);
+  asm volatile("red.release.sys.global.add.u32 [%0], 1;" ::"l"(cnt) : "memory");
+}
+// A skipped pass (convergence flag set) still arrives once per edge, so that the cumulative
+// arrival counts stay E per epoch on every rank.
+__device__ __forceinline__ void peer_skip(const GnPeerOut& peer) {
+  if (peer.world > 0 && blockIdx.x == 0 && threadIdx.x < peer.world) peer_arrive(peer, threadIdx.x);
+}
+
 template <int THREADS, int BAR = 0>
 __device__ __forceinline__ void edge_epilogue(float (&S)[28], float (&v)[7], const Sim3f& Ti,
                                               int e, int chunk, int nchunks, int stride,
                                               float* __restrict__ partials,
                                               int32_t* __restrict__ tickets,
-                                              double* __restrict__ edge_blocks) {
+                                              double* __restrict__ edge_blocks,
+                                              const GnPeerOut& peer) {
   __shared__ float warp_part[THREADS / 32][kGnBlock];
   __shared__ int is_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -334,20 +346,37 @@ __device__ __forceinline__ void edge_epilogue(float (&S)[28], float (&v)[7], con
     MS[threadIdx.x] = acc;
   }
   epi_sync<THREADS, BAR>();
-  double* __restrict__ out = edge_blocks + (size_t)e * kGnBlock;
+  int slot = -1;
+  double acc = 0.0;
   if (threadIdx.x < 49) {
     const int r = threadIdx.x / 7, cc = threadIdx.x % 7;
     if (cc >= r) {
-      double acc = 0.0;
       for (int b = 0; b < 7; ++b) acc += MS[r * 7 + b] * Md[cc * 7 + b];
-      out[r * 7 - r * (r - 1) / 2 + (cc - r)] = acc;
+      slot = r * 7 - r * (r - 1) / 2 + (cc - r);
     }
   } else if (threadIdx.x < 56) {
     const int r = threadIdx.x - 49;
-    double acc = 0.0;
     for (int a = 0; a < 7; ++a) acc += Md[r * 7 + a] * Sd[28 + a];
-    out[28 + r] = acc;
+    slot = 28 + r;
   }
+  if (peer.world <= 0) {
+    if (slot >= 0) edge_blocks[(size_t)e * kGnBlock + slot] = acc;
+    return;
+  }
+  // Multi-GPU: the exchange step is fused here.  The edge's 35 values go straight
+  // into EVERY rank's copy of the global per-edge block array over NVLink peer memory, then
+  // one release-add per rank on its arrival counter; the consumer (the tile build of the
+  // Cholesky, gn_chol_flow.cu) waits for the counter and assembles in fixed edge order, so all
+  // ranks hold bit-identical systems.  280 bytes per edge per rank instead of an all-reduce of
+  // the dense [H | g].
+  if (slot >= 0) {
+    const size_t at = peer.eb_offset + ((size_t)(peer.edge_base + e) * kGnBlock + slot) * sizeof(double);
+    for (int r = 0; r < peer.world; ++r)
+      *reinterpret_cast<double*>(static_cast<char*>(peer.bufs[r]) + at) = acc;
+    __threadfence_system();
+  }
+  epi_sync<THREADS, BAR>();
+  if (threadIdx.x < peer.world) peer_arrive(peer, threadIdx.x);
 }
 
 template <int MODE>
@@ -358,8 +387,12 @@ gn_accumulate_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
                      const int32_t* __restrict__ jj_row, const int64_t* __restrict__ idx,
                      const uint8_t* __restrict__ valid_match, const float* __restrict__ Q, int N,
                      int pts_per_cta, float* __restrict__ partials, int32_t* __restrict__ tickets,
-                     double* __restrict__ edge_blocks, const int32_t* __restrict__ done) {
-  if (done != nullptr && *done != 0) return;
+                     double* __restrict__ edge_blocks, const int32_t* __restrict__ done,
+                     const GnPeerOut peer) {
+  if (done != nullptr && *done != 0) {
+    peer_skip(peer);
+    return;
+  }
   const int e = blockIdx.y;
   const int chunk = blockIdx.x;
   const int nchunks = gridDim.x;
@@ -430,7 +463,8 @@ gn_accumulate_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
       point_terms<MODE>(c, S, v, Xi[r], Xj[r], q[r], ci[r], cj[r], vm[r], ind[r]);
   }
 
-  edge_epilogue<kThreads>(S, v, Ti, e, chunk, nchunks, nchunks, partials, tickets, edge_blocks);
+  edge_epilogue<kThreads>(S, v, Ti, e, chunk, nchunks, nchunks, partials, tickets, edge_blocks,
+                          peer);
 }
 
 // ---------------------------------------------------------------------------
@@ -690,8 +724,11 @@ gn_accumulate_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
                                  const float* __restrict__ Q, int N, int pts_per_cta,
                                  float* __restrict__ partials, int32_t* __restrict__ tickets,
                                  double* __restrict__ edge_blocks,
-                                 const int32_t* __restrict__ done) {
-  if (done != nullptr && *done != 0) return;
+                                 const int32_t* __restrict__ done, const GnPeerOut peer) {
+  if (done != nullptr && *done != 0) {
+    peer_skip(peer);
+    return;
+  }
   extern __shared__ __align__(128) unsigned char stage_raw[];
   __shared__ __align__(8) uint64_t full_bar[kStages];
   __shared__ __align__(8) uint64_t empty_bar[kStages];
@@ -877,7 +914,8 @@ gn_accumulate_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
   for (int k = 0; k < 28; ++k) S[k] = S2[k].x + S2[k].y;
 #pragma unroll
   for (int k = 0; k < 7; ++k) v[k] = v2[k].x + v2[k].y;
-  edge_epilogue<kRaysThreads>(S, v, Ti, e, chunk, nchunks, nchunks, partials, tickets, edge_blocks);
+  edge_epilogue<kRaysThreads>(S, v, Ti, e, chunk, nchunks, nchunks, partials, tickets,
+                              edge_blocks, peer);
 }
 
 
@@ -944,8 +982,10 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
                          const int32_t* ii_row, const int32_t* jj_row, const int64_t* idx,
                          const uint8_t* valid, const float* Q, int K, int N, int E,
                          float* partials, int32_t* tickets, double* edge_blocks,
-                         const int32_t* done, cudaStream_t s) {
+                         const int32_t* done, cudaStream_t s, const GnPeerOut* peer_out) {
   if (E == 0) return FRODO_OK;
+  GnPeerOut peer = {};
+  if (peer_out != nullptr) peer = *peer_out;
   const int ppc = gn_pts_per_cta(E, N);
   const int nchunks = (N + ppc - 1) / ppc;
   dim3 grid(nchunks > 0 ? nchunks : 1, E);
@@ -973,15 +1013,15 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
     if (prm.mode == FRODO_GN_RAYS)
       gn_accumulate_packed_kernel<FRODO_GN_RAYS><<<grid, kRaysThreads, smem, s>>>(
           prm, Twc, Kmat, xc, xp, ii_row, jj_row, idx, valid, Q, N, ppc, partials, tickets,
-          edge_blocks, done);
+          edge_blocks, done, peer);
     else if (prm.mode == FRODO_GN_POINTS)
       gn_accumulate_packed_kernel<FRODO_GN_POINTS><<<grid, kRaysThreads, smem, s>>>(
           prm, Twc, Kmat, xc, xp, ii_row, jj_row, idx, valid, Q, N, ppc, partials, tickets,
-          edge_blocks, done);
+          edge_blocks, done, peer);
     else
       gn_accumulate_packed_kernel<FRODO_GN_CALIB><<<grid, kRaysThreads, smem, s>>>(
           prm, Twc, Kmat, xc, xp, ii_row, jj_row, idx, valid, Q, N, ppc, partials, tickets,
-          edge_blocks, done);
+          edge_blocks, done, peer);
     FRODO_CUDA_TRY(cudaGetLastError());
     return FRODO_OK;
   }
@@ -989,17 +1029,17 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
     case FRODO_GN_RAYS:
       gn_accumulate_kernel<FRODO_GN_RAYS><<<grid, kThreads, 0, s>>>(
           prm, Twc, Xs, Cs, Kmat, ii_row, jj_row, idx, valid, Q, N, ppc, partials, tickets,
-          edge_blocks, done);
+          edge_blocks, done, peer);
       break;
     case FRODO_GN_POINTS:
       gn_accumulate_kernel<FRODO_GN_POINTS><<<grid, kThreads, 0, s>>>(
           prm, Twc, Xs, Cs, Kmat, ii_row, jj_row, idx, valid, Q, N, ppc, partials, tickets,
-          edge_blocks, done);
+          edge_blocks, done, peer);
       break;
     case FRODO_GN_CALIB:
       gn_accumulate_kernel<FRODO_GN_CALIB><<<grid, kThreads, 0, s>>>(
           prm, Twc, Xs, Cs, Kmat, ii_row, jj_row, idx, valid, Q, N, ppc, partials, tickets,
-          edge_blocks, done);
+          edge_blocks, done, peer);
       break;
     default:
       set_error("unknown GN mode %d", prm.mode);

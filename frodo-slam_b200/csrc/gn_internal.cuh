@@ -55,13 +55,25 @@ int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float*
 // One keyframe (X [N,3], C [N]) into row `slot` of a packed region laid out for K_total keyframes.
 int launch_gn_pack_slot(const float* X, const float* C, int K_total, int slot, int N, float* XC,
                         cudaStream_t s);
+// Multi-GPU output of the accumulate kernels (world = 0: plain local edge_blocks).  bufs[r]
+// = base of rank r's peer-mapped exchange buffer; the per-edge blocks of the current epoch live
+// at eb_offset inside it, indexed by GLOBAL edge number (edge_base + local edge), the arrival
+// counter (u32) at cnt_offset.
+struct GnPeerOut {
+  void* const* bufs;  // device table [world]
+  size_t eb_offset;
+  size_t cnt_offset;
+  int world;
+  int edge_base;
+};
 // XC: pointmaps packed by launch_gn_pack_points (XC [K][N] float4, then XP), or NULL.
 int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const float* Xs,
                          const float* Cs, const float* Kmat, const float* XC,
                          const int32_t* ii_row,
                          const int32_t* jj_row, const int64_t* idx, const uint8_t* valid,
                          const float* Q, int K, int N, int E, float* partials, int32_t* tickets,
-                         double* edge_blocks, const int32_t* done, cudaStream_t s);
+                         double* edge_blocks, const int32_t* done, cudaStream_t s,
+                         const GnPeerOut* peer_out = nullptr);
 int launch_gn_assemble(const double* edge_blocks, const int32_t* ii_row, const int32_t* jj_row,
                        int E, int K, int num_fix, double* Hg, const int32_t* done, cudaStream_t s);
 // Where the normal equations of one iteration are: the dense fp64 [H | g] (`Hg`, valid when
@@ -72,9 +84,13 @@ struct GnSystem {
   double* Hg;
   bool dense;
   const double* edge_blocks;
-  const int32_t* ii_row;
+  const int32_t* ii_row;  // negative rows mark padding entries (skipped)
   const int32_t* jj_row;
   int E;
+  // multi-GPU: the blocks are complete once *wait_counter has reached wait_target (arrivals of
+  // every rank's accumulate kernel, gn_accumulate.cu); NULL = no wait
+  const uint32_t* wait_counter = nullptr;
+  uint32_t wait_target = 0;
 };
 // n_max: the system size the Cholesky scratch was laid out and initialised for (7 x keyframes).
 int launch_gn_solve_retract(const GnSystem& sys, float* Twc, float* dx, int K, int num_fix,
@@ -86,6 +102,10 @@ int gn_chol_scratch_init(double* scratch, int n_max, cudaStream_t s);
 int launch_chol_flow(const double* Hg, const double* edge_blocks, const int32_t* ii_row,
                      const int32_t* jj_row, int E, float* Twc, float* dx, int K, int num_fix,
                      float delta_thresh, int32_t* done, int32_t* info, double* chol_scratch,
-                     int n_max, int* handled, cudaStream_t s, const int32_t* pose_rows = nullptr);
+                     int n_max, int* handled, cudaStream_t s, const int32_t* pose_rows = nullptr,
+                     const uint32_t* wait_counter = nullptr, uint32_t wait_target = 0);
+// Spins (one thread, bounded) until *counter has reached target; on time-out bumps info[1].
+int launch_gn_peer_wait(const uint32_t* counter, uint32_t target, const int32_t* done,
+                        int32_t* info, cudaStream_t s);
 
 }  // namespace frodo

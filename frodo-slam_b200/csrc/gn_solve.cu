@@ -292,6 +292,10 @@ int launch_gn_solve_retract(const GnSystem& sys, float* Twc, float* dx, int K, i
   double* Hg = sys.Hg;
   auto need_dense = [&]() -> int {
     if (sys.dense) return FRODO_OK;
+    if (sys.wait_counter != nullptr) {
+      const int wrc = launch_gn_peer_wait(sys.wait_counter, sys.wait_target, done, info, s);
+      if (wrc != FRODO_OK) return wrc;
+    }
     return launch_gn_assemble(sys.edge_blocks, sys.ii_row, sys.jj_row, sys.E, K, num_fix, Hg, done,
                               s);
   };
@@ -308,7 +312,8 @@ int launch_gn_solve_retract(const GnSystem& sys, float* Twc, float* dx, int K, i
   int handled = 0;
   int rc = launch_chol_flow(sys.dense ? Hg : nullptr, sys.edge_blocks, sys.ii_row, sys.jj_row,
                             sys.E, Twc, dx, K, num_fix, delta_thresh, done, info, chol_scratch,
-                            n_max, &handled, s, pose_rows);
+                            n_max, &handled, s, pose_rows, sys.dense ? nullptr : sys.wait_counter,
+                            sys.wait_target);
   if (rc != FRODO_OK || handled) return rc;
   // fallback: no cooperative launch on this device, no scratch, or beyond the tile plan
   rc = need_dense();

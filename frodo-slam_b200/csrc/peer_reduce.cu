@@ -14,7 +14,7 @@
 // only overwrite the buffer of epoch e when it assembles epoch e+2, i.e. after it completed the
 // reduction of epoch e+1, which every peer entered only after finishing its reads of epoch e.
 // `done` (the solver's convergence flag, identical on all ranks) skips the whole step.
-#include "common.cuh"
+#include "gn_internal.cuh"
 
 namespace frodo {
 
@@ -46,7 +46,8 @@ peer_allreduce_kernel(const double* const* __restrict__ bufs, uint32_t* const* _
   }
   if (tid < world) {
     const uint32_t* mine = pads[rank] + pad_slot0 + tid;
-    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+    const long long t0 = clock64();  // bounded: a dead peer must not hang this GPU
+    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0 && clock64() - t0 < 8000000000LL) {
     }
   }
   __syncthreads();
@@ -82,7 +83,34 @@ peer_allreduce_kernel(const double* const* __restrict__ bufs, uint32_t* const* _
   }
 }
 
+// Consumer-side wait of the fused exchange (gn_accumulate.cu pushes per-edge blocks to every
+// rank and bumps its arrival counter): used by the solve paths that do not wait inside their own
+// kernel (small systems, the single-CTA fallback).  Bounded spin: a dead peer must not hang the GPU.
+__global__ void peer_wait_kernel(const uint32_t* __restrict__ counter, uint32_t target,
+                                 const int32_t* __restrict__ done, int32_t* __restrict__ info) {
+  if (done != nullptr && *done != 0) return;
+  const long long t0 = clock64();
+  uint32_t v;
+  for (;;) {
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+    if ((int32_t)(v - target) >= 0) break;
+    if (clock64() - t0 > 8000000000LL) {  // ~4 s
+      if (info != nullptr) atomicAdd(info + 1, 1);
+      break;
+    }
+    __nanosleep(40);
+  }
+  v = ld_acquire_sys(counter);
+}
+
 }  // namespace
+
+int launch_gn_peer_wait(const uint32_t* counter, uint32_t target, const int32_t* done,
+                        int32_t* info, cudaStream_t s) {
+  peer_wait_kernel<<<1, 1, 0, s>>>(counter, target, done, info);
+  FRODO_CUDA_TRY(cudaGetLastError());
+  return FRODO_OK;
+}
 
 int launch_peer_allreduce(const void* bufs_dev, const void* pads_dev, size_t buf_offset,
                           int pad_slot0, int rank, int world, uint32_t epoch, double* out, size_t n,

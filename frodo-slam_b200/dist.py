@@ -1,10 +1,16 @@
 """Edge-sharded multi-GPU Gauss-Newton: one process per GPU, keyframe
 poses/pointmaps replicated, the directed edges split into contiguous per-rank slices.
-Each iteration every rank accumulates its edges into a local dense fp64 [H | g], the
-systems are summed with one all-reduce (NCCL over NVLink on GPUs, gloo on CPU-only
-test runs of the host logic), and every rank runs the identical Cholesky solve and
-pose retraction -- bit-identical inputs give bit-identical poses, so no broadcast of
-dx is needed.  The reference has no multi-GPU path."""
+
+Fast path (NVLink peer memory available): the whole solve is ONE C-ABI call,
+``frodo_gauss_newton_sharded``.  The exchange step is fused into the accumulate kernel: the last
+CTA of every edge stores the edge's 35 fp64 values into every rank's copy of the global per-edge
+block array and bumps that rank's arrival counter; the Cholesky's tile build waits for the
+counter and assembles in fixed edge order, so all ranks hold bit-identical systems, run the
+identical solve and keep bit-identical poses with no broadcast of dx.
+
+Fallback (no peer mapping, ``FRODO_PEER_REDUCE=0``, gloo on CPU-only test runs of the host
+logic): every rank assembles its edges into a dense fp64 [H | g], one all-reduce (NCCL / gloo)
+sums them, every rank solves.  The reference has no multi-GPU path."""
 import ctypes
 import os
 
@@ -12,7 +18,7 @@ import torch
 import torch.distributed as dist
 
 from . import _lib
-from ._lib import OdomTerms
+from ._lib import GnPeer, OdomTerms
 from .backends import _gn_validate, _ptr, _stream
 
 
@@ -56,6 +62,54 @@ def _peer_state(numel, dev, group):
     return st
 
 
+_BLOCK_CACHE = {}
+
+
+def _group_key(group):
+    pg = group if group is not None else dist.group.WORLD
+    try:
+        return (pg.group_name, tuple(dist.get_process_group_ranks(pg)))
+    except Exception:
+        return (id(pg),)
+
+
+def _block_exchange_state(max_edges, dev, group):
+    """Peer-mapped per-edge block arrays + arrival counters for ``frodo_gauss_newton_sharded``
+    (layout: include/frodo_b200.h, struct frodo_gn_peer), or None when symmetric memory cannot
+    serve this group.  Whether the fast path is used is agreed by ALL ranks (a MIN all-reduce of
+    the per-rank outcome), so one rank can never spin on peers that fell back to NCCL."""
+    if dev.type != "cuda":
+        return None
+    key = (_group_key(group), dev.index, int(max_edges))
+    if key in _BLOCK_CACHE:
+        return _BLOCK_CACHE[key]
+    pg = group if group is not None else dist.group.WORLD
+    world = dist.get_world_size(pg)
+    st = None
+    want = os.environ.get("FRODO_PEER_REDUCE", "1") != "0" and world <= 16
+    if want:
+        try:
+            import torch.distributed._symmetric_memory as symm
+            nbytes = _lib.load().frodo_gn_peer_buffer_bytes(int(max_edges))
+            buf = symm.empty(nbytes // 8, dtype=torch.float64, device=dev)
+            buf.zero_()
+            hdl = symm.rendezvous(buf, pg)
+            st = dict(buf=buf, hdl=hdl, bufs_dev=int(hdl.buffer_ptrs_dev), epoch=0,
+                      arrivals=[0, 0], rank=dist.get_rank(pg), world=world,
+                      max_edges=int(max_edges))
+            torch.cuda.synchronize(dev)
+        except Exception as exc:  # no peer mapping on this system / build
+            st = None
+            if os.environ.get("FRODO_PEER_REDUCE_DEBUG"):
+                print(f"[frodo] block exchange unavailable, using all-reduce: {exc!r}", flush=True)
+    ok = torch.tensor([1 if st is not None else 0], device=dev, dtype=torch.int32)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=pg)  # also the barrier after zeroing
+    if int(ok.item()) == 0:
+        st = None
+    _BLOCK_CACHE[key] = st
+    return st
+
+
 def edge_slice(num_edges, rank, world):
     """Contiguous balanced slice [lo, hi) of the edge list owned by `rank`."""
     base, rem = divmod(num_edges, world)
@@ -94,9 +148,21 @@ class ShardedGaussNewton:
             self._ids = torch.unique(torch.cat([ii, jj]), sorted=True)  # for set_odometry
             # the exchange step: one kernel over NVLink peer memory (csrc/peer_reduce.cu) when
             # torch can map the ranks' buffers into each other, NCCL's all-reduce otherwise
+            # exchange step: fused into the accumulate kernel over NVLink peer memory
+            # (frodo_gauss_newton_sharded) when every rank can map its peers' buffers; otherwise
+            # a dense all-reduce (peer kernel of csrc/peer_reduce.cu or NCCL / gloo)
             self.peer = None
+            self.blocks = None
+            self.E = E
+            self.ii_row_all, self.jj_row_all = ii_row, jj_row
             if dist.is_initialized() and dist.get_world_size(group) > 1 and n > 0:
-                self.peer = _peer_state((n + 1) * n, dev, group)
+                if os.environ.get("FRODO_BLOCK_EXCHANGE", "1") != "0":
+                    self.blocks = _block_exchange_state(E, dev, group)
+                if self.blocks is None:
+                    self.peer = _peer_state((n + 1) * n, dev, group)
+            # workspace of the one-call driver: sized for all E edges
+            self.nbytes_all = lib.frodo_gn_workspace_bytes(self.num_kf, max(E, 1), self.N)
+            self.ws_all = None
             self.odom = None
             self.ii_row = ii_row[lo:hi].contiguous()
             self.jj_row = jj_row[lo:hi].contiguous()
@@ -136,7 +202,42 @@ class ShardedGaussNewton:
         t.blocks, t.blocks_bytes = blocks.data_ptr(), nb
         self.odom = (t, (oi, oj, rank, Tij, sb, blocks))
 
+    def _solve_one_call(self, max_iter, delta_thresh):
+        """frodo_gauss_newton_sharded: the whole loop in one C-ABI call (world 1: no exchange)."""
+        lib, dev = self.lib, self.Twc.device
+        with torch.cuda.device(dev):
+            if self.ws_all is None:
+                self.ws_all = torch.empty(self.nbytes_all, dtype=torch.uint8, device=dev)
+            self.flags.zero_()
+            peer = None
+            b = self.blocks
+            if b is not None:
+                peer = GnPeer()
+                peer.peer_buffers = b["bufs_dev"]
+                peer.local_buffer = b["buf"].data_ptr()
+                peer.world, peer.rank, peer.max_edges = b["world"], b["rank"], b["max_edges"]
+                peer.epoch0 = b["epoch"] & 0xFFFFFFFF
+                peer.arrivals0[0] = b["arrivals"][0] & 0xFFFFFFFF
+                peer.arrivals0[1] = b["arrivals"][1] & 0xFFFFFFFF
+            _lib.check(lib.frodo_gauss_newton_sharded(
+                ctypes.byref(self.params), _ptr(self.Twc), _ptr(self.Xs), _ptr(self.Cs),
+                _ptr(self.K), _ptr(self.ii_row_all), _ptr(self.jj_row_all), self.E, self.lo,
+                self.hi, _ptr(self.idx), _ptr(self.valid), _ptr(self.Q), self.num_kf, self.N,
+                self.num_fix, int(max_iter), float(delta_thresh),
+                ctypes.byref(peer) if peer is not None else None,
+                ctypes.byref(self.odom[0]) if self.odom is not None else None, _ptr(self.dx),
+                ctypes.c_void_p(self.flags.data_ptr()), ctypes.c_void_p(self.flags.data_ptr() + 4),
+                _ptr(self.ws_all), self.nbytes_all, _stream()))
+            if b is not None:  # advance the exchange state exactly as the C side did
+                for it in range(int(max_iter)):
+                    b["epoch"] += 1
+                    b["arrivals"][b["epoch"] & 1] += self.E
+        return self.dx
+
     def solve(self, max_iter, delta_thresh):
+        multi = dist.is_initialized() and dist.get_world_size(self.group) > 1
+        if self.blocks is not None or (not multi and os.environ.get("FRODO_ONE_CALL", "1") != "0"):
+            return self._solve_one_call(max_iter, delta_thresh)
         lib, dev = self.lib, self.Twc.device
         with torch.cuda.device(dev):
             st = _stream()

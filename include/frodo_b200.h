@@ -290,6 +290,53 @@ int frodo_gn_add_odom(const frodo_gn_odom_terms* terms, const float* Twc,
  *   epoch: strictly increasing (by one) per call, identical on all ranks, never 0.
  *   out [n] f64: local result.  `done` (may be NULL): when non-zero the call is skipped (it must
  *     hold the same value on all ranks: it does, the poses are bit-identical). */
+/* The edge-sharded solve in ONE call (the reference has no multi-GPU path): every
+ * rank passes the replicated poses / pointmaps, the keyframe ranks of ALL E edges (ii_row, jj_row
+ * from frodo_gn_edge_index on the full edge list) and the data of its own contiguous slice
+ * [edge_lo, edge_hi) (idx_local, valid_local, Q_local: [edge_hi - edge_lo, N]).  Per iteration:
+ *   accumulate  this rank's edges; the last CTA of every edge stores the edge's 35 fp64 values
+ *               into EVERY rank's copy of the global per-edge block array over NVLink peer
+ *               memory and bumps that rank's arrival counter (release, system scope): the
+ *               exchange is fused into the producer, 280 bytes per edge per rank;
+ *   solve       the Cholesky's tile build waits until the local counter shows all E edges of
+ *               this epoch (acquire), assembles in fixed edge order -- bit-identical systems on
+ *               all ranks -- factors, retracts; every rank runs it redundantly, so the poses
+ *               stay bit-identical with no broadcast.
+ * No host synchronisation and no launch from Python inside the loop.
+ * peer (NULL or world <= 1: single GPU, same result as frodo_gauss_newton):
+ *   peer_buffers  device table [world] of the ranks' peer-mapped exchange buffers (e.g. torch
+ *                 symmetric memory's buffer_ptrs_dev), local_buffer this rank's own;
+ *                 each buffer holds 2 * max_edges * 35 doubles (blocks of even / odd epochs)
+ *                 followed by 2 x 128 bytes of arrival counters, all ZERO when first used;
+ *   epoch0        number of iterations ever run on these buffers (identical on all ranks),
+ *   arrivals0[p]  arrivals so far on the counter of parity p (E per epoch of that parity);
+ *                 the caller advances both after the call: epoch0 += max_iter, arrivals0[p] +=
+ *                 E x (epochs of parity p in this call).  Iterations skipped after convergence
+ *                 still arrive, so these counts do not depend on the data.
+ * A wait that sees no progress for ~4 s gives up (dead peer), counts a failure in info[1] and
+ * lets the kernel finish on what it has.
+ * done (device int32, must be zero on entry) and info (device int32[2]) as in
+ * frodo_gn_solve_retract; workspace of frodo_gn_workspace_bytes(K, E, N) bytes (ALL E edges). */
+typedef struct frodo_gn_peer {
+  const void* peer_buffers;
+  void* local_buffer;
+  int world;
+  int rank;
+  int max_edges;
+  uint32_t epoch0;
+  uint32_t arrivals0[2];
+} frodo_gn_peer;
+size_t frodo_gn_peer_buffer_bytes(int max_edges);
+int frodo_gauss_newton_sharded(const frodo_gn_params* params, float* Twc, const float* Xs,
+                               const float* Cs, const float* Kmat, const int32_t* ii_row,
+                               const int32_t* jj_row, int E, int edge_lo, int edge_hi,
+                               const int64_t* idx_local, const uint8_t* valid_local,
+                               const float* Q_local, int K, int N, int num_fix, int max_iter,
+                               float delta_thresh, const frodo_gn_peer* peer,
+                               const frodo_gn_odom_terms* odom, float* dx, int32_t* done,
+                               int32_t* info, void* workspace, size_t workspace_bytes,
+                               frodo_stream_t stream);
+
 int frodo_gn_peer_allreduce(const void* peer_buffers, const void* peer_signal_pads,
                             size_t buffer_offset_bytes, int signal_slot0, int rank, int world,
                             uint32_t epoch, double* out, size_t n, const int32_t* done,
