@@ -285,8 +285,10 @@ def run_match_pipeline(device, B, steps, warmup, peak):
 
 
 def cpu_baseline_gn(g_np, seconds=12.0):
-    """Oracle port (C, OpenMP, all host threads) on a bounded sample of the same workload:
-    per-edge accumulation of a subset of the 256 edges; iters/s extrapolated to the full graph."""
+    """Oracle port (C, OpenMP, all host threads) on a bounded sample of the same workload: the
+    per-edge accumulation of a subset of the 256 edges (extrapolated to all of them) PLUS the
+    assembly and the Cholesky solve of the full 441 x 441 system -- a whole iteration, as
+    gn_kernels.cu:949-992 runs it."""
     from frodo_slam_b200 import synth
     from oracle import oracle
     gp = synth.GN_PARAMS
@@ -297,17 +299,91 @@ def cpu_baseline_gn(g_np, seconds=12.0):
     t0 = time.perf_counter()
     passes = 0
     while True:
-        oracle.edge_blocks("rays", g_np["Twc"], g_np["Xs"], g_np["Cs"], ie[:ns], je[:ns],
-                           g_np["idx"][:ns], g_np["valid"][:ns], g_np["Q"][:ns], gp["sigma_ray"],
-                           gp["sigma_dist"], gp["C_conf"], gp["Q_conf"])
+        Hs, gs = oracle.edge_blocks("rays", g_np["Twc"], g_np["Xs"], g_np["Cs"], ie[:ns], je[:ns],
+                                    g_np["idx"][:ns], g_np["valid"][:ns], g_np["Q"][:ns],
+                                    gp["sigma_ray"], gp["sigma_dist"], gp["C_conf"], gp["Q_conf"])
         passes += 1
         if time.perf_counter() - t0 > seconds:
             break
     dt = (time.perf_counter() - t0) / passes
-    t_iter = dt * E / ns
+    # assembly + solve of the FULL system (the sampled blocks tiled over all edges: timing only)
+    rep = (E + ns - 1) // ns
+    Hs_all = np.tile(Hs, (1, rep, 1, 1))[:, :E]
+    gs_all = np.tile(gs, (1, rep, 1))[:, :E]
+    K = g_np["Xs"].shape[0]
+    t1 = time.perf_counter()
+    H, gvec = oracle.assemble(Hs_all, gs_all, ie, je, K, gp["num_fix"])
+    H = H + 1e-3 * np.abs(H).max() * np.eye(H.shape[0])  # tiled blocks: keep it factorisable
+    oracle.chol_solve(H, gvec)
+    t_solve = time.perf_counter() - t1
+    t_iter = dt * E / ns + t_solve
     return {"value": 1.0 / t_iter, "unit": "iters/s", "cores": cores, "kind": "port",
-            "sample": f"{ns} of {E} edges x {N_PTS} points, {passes} passes, accumulation only "
-                      f"(solve excluded), extrapolated x{E / ns:.0f}"}
+            "sample": f"{ns} of {E} edges x {N_PTS} points, {passes} passes (accumulation "
+                      f"extrapolated x{E / ns:.0f}: {dt * E / ns:.2f} s) + assembly and Cholesky of "
+                      f"the full {H.shape[0]}x{H.shape[0]} system ({t_solve * 1e3:.1f} ms)"}
+
+
+def cpu_baseline_gn_torch(g_np, edges=4):
+    """The PyTorch-CPU formulation (oracle/torch_cpu.py, SURVEY 8(d) "C1") of one whole
+    gauss_newton_rays iteration on all host cores: accumulation of `edges` of the 256 edges
+    (extrapolated), assembly and Cholesky solve of the full system."""
+    from frodo_slam_b200 import synth
+    from oracle import torch_cpu
+    gp = synth.GN_PARAMS
+    cores = torch_cpu.use_all_cores()
+    t = {k: torch.from_numpy(np.ascontiguousarray(v)) for k, v in g_np.items()}
+    E = t["ii"].shape[0]
+    valid = t["valid"].bool()
+    args = (t["Twc"], t["Xs"], t["Cs"], t["ii"], t["jj"], t["idx"], valid, t["Q"], gp["sigma_ray"],
+            gp["sigma_dist"], gp["C_conf"], gp["Q_conf"], gp["num_fix"])
+    sel = list(range(0, E, max(1, E // edges)))[:edges]
+    torch_cpu.gn_rays_system(*args, edges=sel[:1])  # warm-up
+    t0 = time.perf_counter()
+    H, g = torch_cpu.gn_rays_system(*args, edges=sel)
+    t_acc = (time.perf_counter() - t0) * E / len(sel)
+    H = H + 1e-3 * H.abs().max() * torch.eye(H.shape[0], dtype=H.dtype)
+    t1 = time.perf_counter()
+    torch_cpu.gn_solve(H, g)
+    t_solve = time.perf_counter() - t1
+    return {"value": 1.0 / (t_acc + t_solve), "unit": "iters/s", "cores": cores,
+            "kind": "port (PyTorch-CPU formulation)",
+            "sample": f"{len(sel)} of {E} edges x {N_PTS} points (accumulation extrapolated: "
+                      f"{t_acc:.2f} s) + Cholesky solve ({t_solve * 1e3:.1f} ms)"}
+
+
+def cpu_baseline_matching():
+    """BASELINE.json configs[0]: iter_proj + refine_matches on ONE 512x384 pair on the host
+    cores, C/OpenMP oracle port and PyTorch-CPU formulation."""
+    from frodo_slam_b200 import synth
+    from oracle import oracle, torch_cpu
+    mp = synth.MATCH_PARAMS
+    d = synth.matching_pairs(1, H_IMG, W_IMG, seed=0)
+    rays, pts, p0 = synth.prep_for_iter_proj(d["X11"], d["X21"])
+    D11 = d["D11"].half().contiguous()
+    D21 = d["D21"].half().reshape(1, N_PTS, -1).contiguous()
+    out = {}
+    t0 = time.perf_counter()
+    p, _ = oracle.iter_proj(rays.numpy(), pts.numpy(), p0.numpy(), mp["max_iter"],
+                            mp["lambda_init"], mp["convergence_thresh"])
+    t1 = time.perf_counter()
+    p1 = torch.from_numpy(p).long()
+    oracle.refine_matches(D11.numpy(), D21.numpy(), p1.numpy(), mp["radius"], mp["dilation_max"])
+    t2 = time.perf_counter()
+    out["c_port"] = {"value": N_PTS / (t2 - t0), "unit": "px-matches/s", "cores": oracle.num_threads(),
+                     "kind": "port", "iter_proj_s": t1 - t0, "refine_matches_s": t2 - t1,
+                     "sample": "one 512x384 pair (configs[0]), whole ops"}
+    cores = torch_cpu.use_all_cores()
+    t0 = time.perf_counter()
+    pt, _ = torch_cpu.iter_proj(rays, pts, p0, mp["max_iter"], mp["lambda_init"],
+                                mp["convergence_thresh"])
+    t1 = time.perf_counter()
+    torch_cpu.refine_matches(D11, D21, pt.long(), mp["radius"], mp["dilation_max"])
+    t2 = time.perf_counter()
+    out["torch_cpu"] = {"value": N_PTS / (t2 - t0), "unit": "px-matches/s", "cores": cores,
+                        "kind": "port (PyTorch-CPU formulation)", "iter_proj_s": t1 - t0,
+                        "refine_matches_s": t2 - t1,
+                        "sample": "one 512x384 pair (configs[0]), whole ops"}
+    return out
 
 
 def run_other_configs(dev, be, iters, quiet=False):
@@ -450,6 +526,11 @@ def main_ours(args):
                                   idx[lo:hi].contiguous(), valid[lo:hi].contiguous(),
                                   Q[lo:hi].contiguous(), lo, hi, gp["num_fix"])
     iters = args.gn_iters
+    exchange = ("none (single GPU)" if world == 1 else
+                "per-edge blocks pushed to every rank from the accumulate kernel (NVLink peer "
+                "memory, 280 B per edge per rank), one C call per solve" if sg.blocks is not None else
+                "dense [H|g] all-reduce: peer-memory kernel" if sg.peer is not None else
+                "dense [H|g] all-reduce: NCCL")
 
     def step():
         Twc.copy_(Twc0)
@@ -662,8 +743,12 @@ def main_ours(args):
             matching["sweep_224x224"] = {k: m224[k] for k in ("value", "unit", "pairs", "resolution",
                                                               "ms_per_step", "iter_proj",
                                                               "refine_matches")}
+    cpu_torch = None
     if g_np is not None:
         cpu = cpu_baseline_gn(g_np)
+        cpu_torch = cpu_baseline_gn_torch(g_np)
+        if matching is not None:
+            matching["cpu_baseline"] = cpu_baseline_matching()
     tracking = run_tracking(dev) if (world == 1 and not args.no_matching) else None
     other = run_other_configs(dev, be, iters) if (world == 1 and not args.no_matching) else None
 
@@ -676,11 +761,12 @@ def main_ours(args):
             "config": {"workload": "configs[2]: 64-keyframe graph, 63 chain + 65 loop-closure edges "
                                    "both directions (E=256), 512x384 pointmaps, gauss_newton_rays, "
                                    f"{iters} iterations per step, delta_thresh=0",
-                       "edges_per_gpu": hi - lo, "sharding": f"edges/{world} + allreduce(H,g)",
+                       "edges_per_gpu": hi - lo, "sharding": f"edges/{world}", "exchange": exchange,
                        "l2": "inputs larger than L2 (2.27 GB streamed per iteration)"},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
+            "roofline": roofline, "cpu_baseline": cpu, "cpu_baseline_torch": cpu_torch,
+            "e2e": e2e, "clocks": clocks,
             "parity": parity,
-            "gpu_launches": args.steps * (1 + 3 * iters),  # pack + (accumulate, assemble, solve)/iter
+            "gpu_launches": args.steps * (1 + 2 * iters),  # pack + (accumulate, solve) per iteration
             "matching": matching,
             "tracking": tracking,
             "other_configs": other,
