@@ -704,7 +704,9 @@ def main_ours(args):
            "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / pipe_steps,
            "steps": pipe_steps,
            "h2d_gbs": h2d / (ms_e2e / pipe_steps * 1e-3) / 1e9,  # PCIe rate the step sustains
-           "bound": "PCIe host->device copy (the solve, 7.5 ms, hides under the 15.5 ms upload)",
+           "bound": (f"PCIe host->device copy ({h2d / 1e6:.0f} MB per step at "
+                     f"{h2d / (ms_e2e / pipe_steps * 1e-3) / 1e9:.0f} GB/s; the solve, "
+                     f"{ms / args.steps:.1f} ms, hides under the upload)"),
            "overlap": "step n+1's host->device copy (copy stream, second buffer set) runs under "
                       "step n's solve; every step copies all inputs and reads its poses back",
            "serial_value": e2e_steps * iters / (ms_serial * 1e-3),

@@ -58,6 +58,7 @@ SIGNATURES = {
     "frodo_iter_proj": (c_int, [c_void_p] * 5 + [c_int] * 5 + [c_float, c_float, c_void_p]),
     "frodo_refine_matches_f16": (c_int, [c_void_p] * 5 + [c_int] * 7 + [c_void_p]),
     "frodo_set_refine_patch": (c_int, [c_int]),
+    "frodo_refine_matches_f64": (c_int, [c_void_p] * 5 + [c_int] * 7 + [c_void_p]),
     "frodo_refine_matches_f32": (c_int, [c_void_p] * 5 + [c_int] * 7 + [c_void_p]),
     "frodo_match_prep": (c_int, [c_void_p] * 6 + [c_int] * 3 + [c_void_p]),
     "frodo_match_occlusion": (c_int, [c_void_p] * 4 + [c_float, c_void_p, c_void_p] + [c_int] * 3 +

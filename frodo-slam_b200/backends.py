@@ -18,7 +18,7 @@ from . import _lib
 from ._lib import GnParams, GN_RAYS, GN_POINTS, GN_CALIB
 
 __all__ = ["iter_proj", "refine_matches", "gauss_newton_rays", "gauss_newton_points",
-           "gauss_newton_calib", "gn_system"]
+           "gauss_newton_calib", "gauss_newton_rays_odom", "gn_system"]
 
 
 def _check_contiguous(**tensors):
@@ -73,8 +73,8 @@ def refine_matches(D11, D21, p1, radius, dilation_max):
     """gn.cpp:137-150 / matching_kernels.cu:88-125.  Returns [p1_new i64 [B,N,2], max_scores [B,N]]."""
     _check_contiguous(D11=D11, D21=D21, p1=p1)
     dev = p1.device
-    if D11.dtype not in (torch.float16, torch.float32):
-        raise RuntimeError(f"refine_matches supports float16 and float32 descriptors, got {D11.dtype}")
+    if D11.dtype not in (torch.float16, torch.float32, torch.float64):
+        raise RuntimeError(f"refine_matches supports float16/32/64 descriptors, got {D11.dtype}")
     _check(D11, "D11", D11.dtype, dev)
     _check(D21, "D21", D11.dtype, dev)
     _check(p1, "p1", torch.int64)
@@ -85,7 +85,8 @@ def refine_matches(D11, D21, p1, radius, dilation_max):
     if D21.shape != (B, N, F) or p1.shape != (B, N, 2):
         raise RuntimeError("expected D11 [B,H,W,F], D21 [B,N,F], p1 [B,N,2]")
     lib = _lib.load()
-    fn = lib.frodo_refine_matches_f16 if D11.dtype == torch.float16 else lib.frodo_refine_matches_f32
+    fn = {torch.float16: lib.frodo_refine_matches_f16, torch.float32: lib.frodo_refine_matches_f32,
+          torch.float64: lib.frodo_refine_matches_f64}[D11.dtype]
     with torch.cuda.device(dev):
         p1_new = torch.empty((B, N, 2), dtype=torch.int64, device=dev)
         scores = torch.empty((B, N), dtype=D11.dtype, device=dev)

@@ -103,6 +103,15 @@ int frodo_refine_matches_f16(const void* D11, const void* D21, const int64_t* p1
                            dilation_max, static_cast<cudaStream_t>(stream));
 }
 
+int frodo_refine_matches_f64(const double* D11, const double* D21, const int64_t* p1,
+                             int64_t* p1_new, double* max_scores, int B, int H, int W, int N,
+                             int F, int radius, int dilation_max, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(B >= 0 && B <= 65535 && N >= 0 && H >= 1 && W >= 1 && F >= 1 && radius >= 0);
+  FRODO_ARG_CHECK(B == 0 || N == 0 || (D11 && D21 && p1 && p1_new && max_scores));
+  return launch_refine_f64(D11, D21, p1, p1_new, max_scores, B, H, W, N, F, radius, dilation_max,
+                           static_cast<cudaStream_t>(stream));
+}
+
 int frodo_set_refine_patch(int patch) { return refine_forced_patch(patch < 0 ? 0 : patch); }
 
 int frodo_refine_matches_f32(const float* D11, const float* D21, const int64_t* p1,

@@ -67,6 +67,10 @@ int launch_refine_f32(const float* D11, const float* D21, const int64_t* p1, int
                       float* scores, int B, int H, int W, int N, int F, int radius, int dil,
                       cudaStream_t s);
 
+int launch_refine_f64(const double* D11, const double* D21, const int64_t* p1, int64_t* p1_new,
+                      double* scores, int B, int H, int W, int N, int F, int radius, int dil,
+                      cudaStream_t s);
+
 int launch_match_prep(const float* X11, const float* X21, const int64_t* idx_init,
                       float* rays_with_grad, float* pts3d_norm, float* p_init, int B, int H, int W,
                       cudaStream_t s);

@@ -926,7 +926,7 @@ gn_accumulate_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
 // pipeline fill and the reduction epilogue).
 int gn_pts_per_cta(int E, int N) {
   const long long cand[] = {2048, 4096, 6144, 8192, 12288, 16384, 24576, 32768};
-  const double slots = (double)kRaysCtasPerSM * kNumSMs;
+  const double slots = (double)kRaysCtasPerSM * num_sms();
   long long best = 2048;
   double best_cost = 1e300;
   for (long long ppc : cand) {
@@ -956,7 +956,8 @@ int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float*
   const int NB = (N + kTilePts - 1) / kTilePts;
   const size_t slots = (size_t)K * NB * kRaysThreads;
   const size_t want = (slots + 255) / 256;
-  const int blocks = (int)(want < (size_t)(8 * kNumSMs) ? want : (size_t)(8 * kNumSMs));
+  const size_t resident = (size_t)8 * (size_t)num_sms();
+  const int blocks = (int)(want < resident ? want : resident);
   float4* xc = reinterpret_cast<float4*>(XC);
   pack_points_kernel<<<blocks, 256, 0, s>>>(Xs, Cs, xc, xc + total, K, N, NB);
   FRODO_CUDA_TRY(cudaGetLastError());

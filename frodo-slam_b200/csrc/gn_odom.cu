@@ -1,10 +1,27 @@
 // Extra terms of gauss_newton_rays_odom (gn.cpp:29-62, gn_kernels.cu:1792-1934): relative-pose
 // (odometry) constraints between keyframes and a per-keyframe scale prior, added to the dense
 // fp64 normal equations after the visual terms have been assembled.
-//   * odom_blocks_kernel: one thread per odometry edge, the fp32 arithmetic of
-//     odom_constraint_kernel_left_perturb_log (:1106-1286; SE3-log residual of
-//     T_meas^-1 * [R_i^T R_j, R_i^T (t_j - t_i) / s_j], anisotropic sigma, Huber, approximate
-//     Ad(T_j^-1) Jacobian with a scale column), writing the full 14x14 block + 14-vector;
+//
+// Residual of one odometry edge (i -> j, measured relative pose [R_m, t_m]; the reference's
+// odom_constraint_kernel_left_perturb_log, :1106-1286):
+//   R_err = R_m^T R_i^T R_j,  phi = Log(R_err),
+//   rho   = J_l(phi)^-1 (R_m^T (R_i^T (t_j - t_i) / s_j) - R_m^T t_m),   r = [rho, phi],
+// weights W = diag(huber(r / sigma) / sigma^2), Jacobian w.r.t. pose j
+//   J_j = [ R_j^T   [-R_j^T t_j]x R_j^T   -R_m^T t_pred ]     (6 x 7, tangent [tau, theta, sigma])
+//         [ 0       R_j^T                  0            ]
+// and J_i = -J_j with its scale column zeroed.  Hence, as for the visual edges (gn_accumulate.cu),
+// ONE symmetric 7x7  S = J_j^T W J_j  and one 7-vector  v = J_j^T W r  carry the whole 14x14 block:
+//   H_jj = S,   H_ii = S with row/column 6 zeroed,   H_ij = -S with ROW 6 zeroed,
+//   g_j = v,    g_i = -v with entry 6 zeroed,
+// which is what odom_blocks_kernel stores (28 + 7 doubles per edge) and odom_add_kernel expands.
+// S and v are fp32 sums over the six residual rows in row order, so every entry is bit-equal to
+// the corresponding entry of the reference's 14x14 product.
+//
+// Parity note: phi goes through acosf(0.5 (trace - 1)), which quantises angles below ~5e-4 rad;
+// one ulp in R_err moves phi by 3e-4 rad at an information of 1e6.  The chain quaternion -> R ->
+// R_err therefore uses explicit _rn intrinsics in the operation order nvcc gives the reference
+// (read from its SASS, restated in oracle/frodo_oracle.c); everything after Log() is
+// well-conditioned and written in this file's own form.
 //   * odom_add_kernel: one CTA per lower 7x7 block of H (like assemble_kernel), visiting the
 //     odometry edges in order (deterministic fp64 sums), SparseBlock::update_lhs/rhs semantics
 //     (:72-122: blocks with a fixed keyframe are skipped), plus the scale prior of
@@ -18,98 +35,93 @@ namespace frodo {
 
 namespace {
 
-constexpr int kOdomBlock = 14 * 14 + 14;
+constexpr int kOdomBlock = kGnBlock;  // 28 upper-triangular entries of S, then v
 
-__device__ __forceinline__ float huber_o(float r) {  // :214-217 (fp64 compare and divide)
-  const float r_abs = fabsf(r);
-  return (double)r_abs < 1.345 ? 1.0f : (float)(1.345 / (double)r_abs);
+struct Rot3 {
+  float m[9];  // row-major
+  __device__ float operator()(int r, int c) const { return m[3 * r + c]; }
+};
+
+// Rotation matrix of a (not renormalised) quaternion xyzw; operation order as in the SASS of the
+// reference's quat_to_rot (:562-574): 1 - 2 y^2 - 2 z^2 -> fma(-z, 2z, fma(-y, 2y, 1)) etc.
+__device__ __forceinline__ Rot3 rot_from_quat(const float* q) {
+  const float x = q[0], y = q[1], z = q[2], w = q[3];
+  const float x2 = __fadd_rn(x, x), y2 = __fadd_rn(y, y), z2 = __fadd_rn(z, z);
+  const float wz = __fmul_rn(w, z2), wy = __fmul_rn(w, y2), wx = __fmul_rn(w, x2);
+  const float ax = __fmaf_rn(-x, x2, 1.0f), ay = __fmaf_rn(-y, y2, 1.0f);
+  Rot3 R;
+  R.m[0] = __fmaf_rn(-z, z2, ay);
+  R.m[1] = __fmaf_rn(y, x2, -wz);
+  R.m[2] = __fmaf_rn(z, x2, wy);
+  R.m[3] = __fmaf_rn(y, x2, wz);
+  R.m[4] = __fmaf_rn(-z, z2, ax);
+  R.m[5] = __fmaf_rn(z, y2, -wx);
+  R.m[6] = __fmaf_rn(z, x2, -wy);
+  R.m[7] = __fmaf_rn(z, y2, wx);
+  R.m[8] = __fmaf_rn(-y, y2, ax);
+  return R;
 }
 
-__device__ void quat_to_rot(const float* q, float* R) {  // :562-574
-  const float qx = q[0], qy = q[1], qz = q[2], qw = q[3];
-  R[0] = 1 - 2 * qy * qy - 2 * qz * qz;
-  R[1] = 2 * qx * qy - 2 * qz * qw;
-  R[2] = 2 * qx * qz + 2 * qy * qw;
-  R[3] = 2 * qx * qy + 2 * qz * qw;
-  R[4] = 1 - 2 * qx * qx - 2 * qz * qz;
-  R[5] = 2 * qy * qz - 2 * qx * qw;
-  R[6] = 2 * qx * qz - 2 * qy * qw;
-  R[7] = 2 * qy * qz + 2 * qx * qw;
-  R[8] = 1 - 2 * qx * qx - 2 * qy * qy;
-}
-
-__device__ void skew(const float* v, float* M) {
-  M[0] = 0;     M[1] = -v[2]; M[2] = v[1];
-  M[3] = v[2];  M[4] = 0;     M[5] = -v[0];
-  M[6] = -v[1]; M[7] = v[0];  M[8] = 0;
-}
-
-__device__ void mat_vec(const float* A, const float* x, float* y) {
-  y[0] = A[0] * x[0] + A[1] * x[1] + A[2] * x[2];
-  y[1] = A[3] * x[0] + A[4] * x[1] + A[5] * x[2];
-  y[2] = A[6] * x[0] + A[7] * x[1] + A[8] * x[2];
-}
-
-__device__ void mat_mat(const float* A, const float* B, float* C) {
+// A^T B without forming the transpose; inner index ascending, one fma per term.
+__device__ __forceinline__ Rot3 mul_tn(const Rot3& A, const Rot3& B) {
+  Rot3 C;
+#pragma unroll
   for (int r = 0; r < 3; ++r)
-    for (int c = 0; c < 3; ++c) {
-      float acc = 0;
-      for (int k = 0; k < 3; ++k) acc += A[r * 3 + k] * B[k * 3 + c];
-      C[r * 3 + c] = acc;
-    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+      C.m[3 * r + c] = __fmaf_rn(A(2, r), B(2, c), __fmaf_rn(A(1, r), B(1, c), __fmul_rn(A(0, r), B(0, c))));
+  return C;
 }
 
-__device__ void transpose(const float* A, float* T) {
-  T[0] = A[0]; T[1] = A[3]; T[2] = A[6];
-  T[3] = A[1]; T[4] = A[4]; T[5] = A[7];
-  T[6] = A[2]; T[7] = A[5]; T[8] = A[8];
+// A^T x; term order (0, 1 first, then 2) as the reference's 3x3 matrix-vector product compiles.
+__device__ __forceinline__ void mul_tv(const Rot3& A, const float* x, float* y) {
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+    y[r] = __fmaf_rn(A(2, r), x[2], __fmaf_rn(A(0, r), x[0], __fmul_rn(A(1, r), x[1])));
 }
 
-// SO(3) logarithm, :1007-1041
-__device__ void rot_to_vec(const float* R, float* omega) {
-  const float trace = R[0] + R[4] + R[8];
-  float cos_angle = 0.5f * (trace - 1.0f);
-  cos_angle = fmaxf(-1.0f, fminf(1.0f, cos_angle));
-  const float angle = acosf(cos_angle);
+__device__ __forceinline__ float huber_weight(float r) {  // :214-217 (fp64 compare and divide)
+  const float a = fabsf(r);
+  return (double)a < 1.345 ? 1.0f : (float)(1.345 / (double)a);
+}
+
+// SO(3) logarithm with the reference's branch thresholds (:1007-1041): zero below 1e-6 rad, the
+// symmetric-part formula within 1e-6 of pi (largest diagonal entry first), else the
+// antisymmetric part scaled by angle / (2 sin angle).
+__device__ void so3_log(const Rot3& R, float* phi) {
+  const float c = fmaxf(-1.0f, fminf(1.0f, 0.5f * ((R(0, 0) + R(1, 1) + R(2, 2)) - 1.0f)));
+  const float angle = acosf(c);
   if (fabsf(angle) < 1e-6f) {
-    omega[0] = omega[1] = omega[2] = 0.0f;
-  } else if (fabsf((float)((double)angle - 3.14159265358979323846)) < 1e-6f) {
-    if (R[0] > R[4] && R[0] > R[8]) {
-      const float sv = 2.0f * sqrtf(R[0] - R[4] - R[8] + 1.0f);
-      omega[0] = 0.5f * sv; omega[1] = (R[3] + R[1]) / sv; omega[2] = (R[2] + R[6]) / sv;
-    } else if (R[4] > R[8]) {
-      const float sv = 2.0f * sqrtf(R[4] - R[0] - R[8] + 1.0f);
-      omega[0] = (R[3] + R[1]) / sv; omega[1] = 0.5f * sv; omega[2] = (R[7] + R[5]) / sv;
-    } else {
-      const float sv = 2.0f * sqrtf(R[8] - R[0] - R[4] + 1.0f);
-      omega[0] = (R[2] + R[6]) / sv; omega[1] = (R[7] + R[5]) / sv; omega[2] = 0.5f * sv;
-    }
-    omega[0] *= angle; omega[1] *= angle; omega[2] *= angle;
-  } else {
-    const float sin_angle = sinf(angle);
-    const float factor = angle / (2.0f * sin_angle);
-    omega[0] = factor * (R[7] - R[5]);
-    omega[1] = factor * (R[2] - R[6]);
-    omega[2] = factor * (R[3] - R[1]);
+    phi[0] = phi[1] = phi[2] = 0.0f;
+    return;
   }
+  if (fabsf((float)((double)angle - 3.14159265358979323846)) < 1e-6f) {
+    const int a = (R(0, 0) > R(1, 1) && R(0, 0) > R(2, 2)) ? 0 : (R(1, 1) > R(2, 2) ? 1 : 2);
+    const int b = a == 0 ? 1 : 0, d = a == 2 ? 1 : 2;  // the other two axes, ascending
+    const float sv = 2.0f * sqrtf(R(a, a) - R(b, b) - R(d, d) + 1.0f);
+    phi[a] = 0.5f * sv * angle;
+    phi[b] = (R(a, b) + R(b, a)) / sv * angle;
+    phi[d] = (R(a, d) + R(d, a)) / sv * angle;
+    return;
+  }
+  const float f = angle / (2.0f * sinf(angle));
+  phi[0] = f * (R(2, 1) - R(1, 2));
+  phi[1] = f * (R(0, 2) - R(2, 0));
+  phi[2] = f * (R(1, 0) - R(0, 1));
 }
 
-// inverse left Jacobian of SO(3), :1044-1074
-__device__ void left_jacobian_inv(const float* omega, float* J_inv) {
-  const float angle = sqrtf(omega[0] * omega[0] + omega[1] * omega[1] + omega[2] * omega[2]);
-  float sk[9];
-  skew(omega, sk);
-  for (int i = 0; i < 9; ++i) J_inv[i] = (i % 4 == 0) ? 1.0f : 0.0f;
-  if (fabsf(angle) < 1e-6f) {
-    for (int i = 0; i < 9; ++i) J_inv[i] -= 0.5f * sk[i];
-  } else {
-    const float angle_sq = angle * angle;
-    const float sin_angle = sinf(angle), cos_angle = cosf(angle);
-    const float factor2 = (1.0f / angle_sq) - ((1.0f + cos_angle) / (2.0f * angle * sin_angle));
-    float sk2[9];
-    mat_mat(sk, sk, sk2);
-    for (int i = 0; i < 9; ++i) J_inv[i] += -0.5f * sk[i] + factor2 * sk2[i];
-  }
+// y = J_l(phi)^-1 x = x - 0.5 phi x x + k phi x (phi x x),  k = 1/a^2 - (1 + cos a) / (2 a sin a)
+// (:1044-1074; k -> 0 term dropped below 1e-6 rad as there).
+__device__ void left_jacobian_inv_apply(const float* phi, const float* x, float* y) {
+  const float a = sqrtf(__fmaf_rn(phi[2], phi[2], __fmaf_rn(phi[0], phi[0], __fmul_rn(phi[1], phi[1]))));
+  const float c1[3] = {phi[1] * x[2] - phi[2] * x[1], phi[2] * x[0] - phi[0] * x[2],
+                       phi[0] * x[1] - phi[1] * x[0]};
+  float k = 0.0f;
+  if (!(fabsf(a) < 1e-6f)) k = (1.0f / (a * a)) - ((1.0f + cosf(a)) / (2.0f * a * sinf(a)));
+  const float c2[3] = {phi[1] * c1[2] - phi[2] * c1[1], phi[2] * c1[0] - phi[0] * c1[2],
+                       phi[0] * c1[1] - phi[1] * c1[0]};
+#pragma unroll
+  for (int r = 0; r < 3; ++r) y[r] = x[r] - 0.5f * c1[r] + k * c2[r];
 }
 
 __global__ void __launch_bounds__(64)
@@ -120,72 +132,82 @@ odom_blocks_kernel(const float* __restrict__ Twc, const float* __restrict__ Tij,
   if (done != nullptr && *done != 0) return;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= Eo) return;
-  const float* Ti = Twc + 8 * odom_ii[idx];
-  const float* Tj = Twc + 8 * odom_jj[idx];
-  float ti[3], tj[3], qi[4], qj[4], tm[3], qm[4];
-  for (int k = 0; k < 3; ++k) { ti[k] = Ti[k]; tj[k] = Tj[k]; tm[k] = Tij[(size_t)stride * idx + k]; }
-  for (int k = 0; k < 4; ++k) { qi[k] = Ti[3 + k]; qj[k] = Tj[3 + k]; qm[k] = Tij[(size_t)stride * idx + 3 + k]; }
-  const float sj = Tj[7];
-  float R_m[9], R_i[9], R_j[9], R_i_T[9], R_j_T[9], R_m_T[9];
-  quat_to_rot(qm, R_m);
-  quat_to_rot(qi, R_i);
-  quat_to_rot(qj, R_j);
-  transpose(R_i, R_i_T);
-  transpose(R_j, R_j_T);
-  transpose(R_m, R_m_T);
-  float R_ij[9];
-  mat_mat(R_i_T, R_j, R_ij);
-  const float t_diff[3] = {tj[0] - ti[0], tj[1] - ti[1], tj[2] - ti[2]};
-  float rit[3];
-  mat_vec(R_i_T, t_diff, rit);
-  const float sj_inv = (sj == 0.0f) ? 1e6f : 1.0f / sj;
-  const float t_pred[3] = {sj_inv * rit[0], sj_inv * rit[1], sj_inv * rit[2]};
-  float t_meas_inv[3];
-  mat_vec(R_m_T, tm, t_meas_inv);
-  t_meas_inv[0] = -t_meas_inv[0]; t_meas_inv[1] = -t_meas_inv[1]; t_meas_inv[2] = -t_meas_inv[2];
-  float R_err[9], rmt[3], t_err[3];
-  mat_mat(R_m_T, R_ij, R_err);
-  mat_vec(R_m_T, t_pred, rmt);
-  for (int k = 0; k < 3; ++k) t_err[k] = rmt[k] + t_meas_inv[k];
-  float r[6], J_inv[9];
-  rot_to_vec(R_err, r + 3);
-  left_jacobian_inv(r + 3, J_inv);
-  mat_vec(J_inv, t_err, r);
-  float Wd[6];
+  const float* Pi = Twc + 8 * odom_ii[idx];
+  const float* Pj = Twc + 8 * odom_jj[idx];
+  const float* M = Tij + (size_t)stride * idx;
+  const float ti[3] = {Pi[0], Pi[1], Pi[2]}, tj[3] = {Pj[0], Pj[1], Pj[2]};
+  const float tm[3] = {M[0], M[1], M[2]};
+  const float qi[4] = {Pi[3], Pi[4], Pi[5], Pi[6]}, qj[4] = {Pj[3], Pj[4], Pj[5], Pj[6]};
+  const float qm[4] = {M[3], M[4], M[5], M[6]};
+  const float sj = Pj[7];
+  const Rot3 Rm = rot_from_quat(qm), Ri = rot_from_quat(qi), Rj = rot_from_quat(qj);
+
+  // ---- residual r = [rho, phi] --------------------------------------------------------------
+  const Rot3 Rerr = mul_tn(Rm, mul_tn(Ri, Rj));
+  const float dt[3] = {__fsub_rn(tj[0], ti[0]), __fsub_rn(tj[1], ti[1]), __fsub_rn(tj[2], ti[2])};
+  float t_pred[3], rm_tp[3], rm_tm[3];
+  mul_tv(Ri, dt, t_pred);
+  const float sj_inv = (sj == 0.0f) ? 1e6f : __fdiv_rn(1.0f, sj);  // :1149 guards a zero scale
+#pragma unroll
+  for (int k = 0; k < 3; ++k) t_pred[k] = __fmul_rn(sj_inv, t_pred[k]);
+  mul_tv(Rm, t_pred, rm_tp);  // also d rho / d sigma_j, up to sign
+  mul_tv(Rm, tm, rm_tm);
+  const float t_err[3] = {__fsub_rn(rm_tp[0], rm_tm[0]), __fsub_rn(rm_tp[1], rm_tm[1]),
+                          __fsub_rn(rm_tp[2], rm_tm[2])};
+  float r[6];
+  so3_log(Rerr, r + 3);
+  left_jacobian_inv_apply(r + 3, t_err, r);
+  float w[6];
   const float info_t = 1.0f / (sigma_t * sigma_t), info_r = 1.0f / (sigma_r * sigma_r);
-  for (int k = 0; k < 3; ++k) Wd[k] = info_t * huber_o(r[k] / sigma_t);
-  for (int k = 3; k < 6; ++k) Wd[k] = info_r * huber_o(r[k] / sigma_r);
-  // J = [J_i | J_j], 6 x 14, J_i = -J_j except for the scale column (zero for pose i)
-  float J[84];
-  for (int k = 0; k < 84; ++k) J[k] = 0.0f;
-  float tj_inv[3], tj_sk[9], drho[9], drho_ds[3];
-  mat_vec(R_j_T, tj, tj_inv);
-  tj_inv[0] = -tj_inv[0]; tj_inv[1] = -tj_inv[1]; tj_inv[2] = -tj_inv[2];
-  skew(tj_inv, tj_sk);
-  mat_mat(tj_sk, R_j_T, drho);
-  mat_vec(R_m_T, t_pred, drho_ds);
-  for (int rr = 0; rr < 3; ++rr) {
-    for (int c = 0; c < 3; ++c) {
-      J[rr * 14 + 7 + c] = R_j_T[rr * 3 + c];
-      J[rr * 14 + 7 + 3 + c] = drho[rr * 3 + c];
-      J[(rr + 3) * 14 + 7 + 3 + c] = R_j_T[rr * 3 + c];
-    }
-    J[rr * 14 + 7 + 6] = -drho_ds[rr];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    w[k] = info_t * huber_weight(r[k] / sigma_t);
+    w[3 + k] = info_r * huber_weight(r[3 + k] / sigma_r);
   }
-  for (int rr = 0; rr < 6; ++rr)
-    for (int c = 0; c < 6; ++c) J[rr * 14 + c] = -J[rr * 14 + 7 + c];
-  double* out = blocks + (size_t)idx * kOdomBlock;
-  for (int a = 0; a < 14; ++a) {
-    float jtw[6];
-    for (int k = 0; k < 6; ++k) jtw[k] = J[k * 14 + a] * Wd[k];
-    for (int b = 0; b < 14; ++b) {
-      float val = 0;
-      for (int k = 0; k < 6; ++k) val += jtw[k] * J[k * 14 + b];
-      out[a * 14 + b] = (double)val;
+
+  // ---- J_j (6 x 7), rows 0-2: [Rj^T | [c]x Rj^T | -Rm^T t_pred], rows 3-5: [0 | Rj^T | 0] ------
+  float cpos[3];  // c = -Rj^T t_j: camera j's origin seen from frame j
+  mul_tv(Rj, tj, cpos);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) cpos[k] = -cpos[k];
+  float J[6][7];
+#pragma unroll
+  for (int rr = 0; rr < 3; ++rr) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float rjt = Rj(c, rr);  // (Rj^T)[rr][c]
+      J[rr][c] = rjt;
+      // row rr of [c]x Rj^T = c[r1] * (Rj^T)[r2][.] - c[r2] * (Rj^T)[r1][.]; the zero entry of
+      // the skew row comes first in the reference's 3-term sum and does not change the bits
+      J[rr][3 + c] = rr == 0 ? __fmaf_rn(cpos[1], Rj(c, 2), __fmul_rn(-cpos[2], Rj(c, 1)))
+                   : rr == 1 ? __fmaf_rn(-cpos[0], Rj(c, 2), __fmul_rn(cpos[2], Rj(c, 0)))
+                             : __fmaf_rn(cpos[0], Rj(c, 1), __fmul_rn(-cpos[1], Rj(c, 0)));
+      J[3 + rr][c] = 0.0f;
+      J[3 + rr][3 + c] = rjt;
     }
-    float val = 0;
-    for (int k = 0; k < 6; ++k) val += jtw[k] * r[k];
-    out[196 + a] = (double)val;
+    J[rr][6] = -rm_tp[rr];
+    J[3 + rr][6] = 0.0f;
+  }
+
+  // ---- S = J^T W J (upper triangle), v = J^T W r: fp32, residual rows in order ---------------
+  double* out = blocks + (size_t)idx * kOdomBlock;
+  int l = 0;
+#pragma unroll
+  for (int a = 0; a < 7; ++a) {
+    float jw[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) jw[k] = __fmul_rn(J[k][a], w[k]);
+#pragma unroll
+    for (int b = a; b < 7; ++b) {
+      float acc = 0.0f;
+#pragma unroll
+      for (int k = 0; k < 6; ++k) acc = __fmaf_rn(jw[k], J[k][b], acc);
+      out[l++] = (double)acc;
+    }
+    float acc = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) acc = __fmaf_rn(jw[k], r[k], acc);
+    out[28 + a] = (double)acc;
   }
 }
 
@@ -205,23 +227,29 @@ odom_add_kernel(const double* __restrict__ blocks, const int32_t* __restrict__ r
   const int r = tid / 7, c = tid % 7;
   const bool is_h = tid < 49, is_g = tid >= 49 && tid < 56;
   double acc = 0.0, acc_t = 0.0;  // (7a+r, 7b+c) and its mirror (7b+c, 7a+r)
+  // entry (r, c) of S for this thread and of its mirror (c, r): the same number, S is symmetric
+  const int lo = min(r, c), hi = max(r, c);
+  const int sidx = is_h ? lo * 7 - lo * (lo - 1) / 2 + (hi - lo) : 0;
+  const bool pose6 = r < 6 && c < 6;  // entry untouched by the scale row / column
   for (int e = 0; e < Eo; ++e) {
     const int io = rows[e] - num_fix, jo = rows[Eo + e] - num_fix;
     const double* B = blocks + (size_t)e * kOdomBlock;
     if (is_h) {
-      if (io >= 0) {
-        if (io == a && io == b) acc += B[r * 14 + c];                       // H_ii
-        if (jo >= 0 && io == a && jo == b) acc += B[r * 14 + 7 + c];        // H_ij
-        if (jo >= 0 && io == b && jo == a) acc_t += B[c * 14 + 7 + r];      // H_ij, mirror
+      const double sv = B[sidx];
+      // H_ii = S without its scale row/column; H_ij = -S without its scale ROW (pose i has no
+      // scale term, pose j has); H_ji = H_ij^T; H_jj = S
+      if (io >= 0 && io == a && io == b && pose6) acc += sv;                         // H_ii
+      if (io >= 0 && jo >= 0) {
+        if (io == a && jo == b && r < 6) acc -= sv;                                   // H_ij
+        if (io == b && jo == a && c < 6) acc_t -= sv;                                 // H_ij, mirror
+        if (jo == a && io == b && c < 6) acc -= sv;                                   // H_ji
+        if (jo == b && io == a && r < 6) acc_t -= sv;                                 // H_ji, mirror
       }
-      if (jo >= 0) {
-        if (io >= 0 && jo == a && io == b) acc += B[(7 + r) * 14 + c];      // H_ji
-        if (io >= 0 && jo == b && io == a) acc_t += B[(7 + c) * 14 + r];    // H_ji, mirror
-        if (jo == a && jo == b) acc += B[(7 + r) * 14 + 7 + c];             // H_jj
-      }
+      if (jo >= 0 && jo == a && jo == b) acc += sv;                                   // H_jj
     } else if (is_g && a == b) {
-      if (io == a) acc += B[196 + (tid - 49)];
-      if (jo == a) acc += B[196 + 7 + (tid - 49)];
+      const int k = tid - 49;
+      if (io == a && k < 6) acc -= B[28 + k];  // g_i = -v without the scale entry
+      if (jo == a) acc += B[28 + k];           // g_j = v
     }
   }
   // scale prior on the diagonal block of keyframe row a + num_fix (:1744-1781)

@@ -55,7 +55,7 @@ solve_retract_kernel(double* __restrict__ A, float* __restrict__ Twc, float* __r
     if (warp == 0) {
       for (int j = 0; j < nb; ++j) {
         const double d = sm.Ld[j][j];
-        if (!(d > 0.0)) {
+        if (!(d > 0.0) || !isfinite(d)) {
           if (lane == 0) sm.fail = 1;
           break;
         }

@@ -248,7 +248,7 @@ match_quality_kernel(const float* __restrict__ Q_src, const float* __restrict__ 
 
 int stream_blocks(size_t work_items) {
   const size_t want = (work_items + 255) / 256;
-  const size_t cap = (size_t)kNumSMs * 8;  // 8 resident CTAs of 256 threads per SM
+  const size_t cap = (size_t)num_sms() * 8;  // 8 resident CTAs of 256 threads per SM
   return (int)(want < cap ? (want > 0 ? want : 1) : cap);
 }
 
@@ -310,7 +310,7 @@ int launch_match_quality(const float* Q_src, const float* Q_dst, const float* C_
   FRODO_CUDA_TRY(cudaMemsetAsync(counts, 0, (size_t)B * 2 * sizeof(int32_t), s));
   if (N == 0) return FRODO_OK;
   int bx = (N + kQualThreads * 4 - 1) / (kQualThreads * 4);
-  const int cap = (kNumSMs * 8 + B - 1) / B;
+  const int cap = (num_sms() * 8 + B - 1) / B;
   if (bx > cap) bx = cap;
   if (bx < 1) bx = 1;
   match_quality_kernel<<<dim3(bx, B), kQualThreads, 0, s>>>(Q_src, Q_dst, C_src, C_dst, idx,

@@ -405,21 +405,31 @@ refine_f16_generic_kernel(const __half* __restrict__ D11, const __half* __restri
   scores[t] = max_score;
 }
 
-// fp32 path: score += a*b is contracted to fma(a, b, score) by nvcc in the reference.
+// fp32 / fp64 path (the reference dispatches AT_DISPATCH_FLOATING_TYPES_AND_HALF,
+// matching_kernels.cu:112): score += a*b is contracted to fma(a, b, score) by nvcc in the
+// reference; max_score starts at numeric_limits<scalar_t>::min().
+template <typename T>
+__device__ __forceinline__ T refine_min_score();
+template <>
+__device__ __forceinline__ float refine_min_score<float>() { return 1.17549435e-38f; }
+template <>
+__device__ __forceinline__ double refine_min_score<double>() { return 2.2250738585072014e-308; }
+
+template <typename T>
 __global__ void __launch_bounds__(128)
-refine_f32_kernel(const float* __restrict__ D11, const float* __restrict__ D21,
+refine_f32_kernel(const T* __restrict__ D11, const T* __restrict__ D21,
                   const int64_t* __restrict__ p1, int64_t* __restrict__ p1_new,
-                  float* __restrict__ scores, int H, int W, int N, int F, int radius,
+                  T* __restrict__ scores, int H, int W, int N, int F, int radius,
                   int dil_max) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   const size_t b = blockIdx.y;
   const size_t t = b * (size_t)N + n;
-  const float* __restrict__ img = D11 + b * (size_t)H * W * F;
-  const float* __restrict__ q = D21 + t * F;
+  const T* __restrict__ img = D11 + b * (size_t)H * W * F;
+  const T* __restrict__ q = D21 + t * F;
   long long u0 = p1[t * 2], v0 = p1[t * 2 + 1];
   long long u_new = u0, v_new = v0;
-  float max_score = 1.17549435e-38f;  // numeric_limits<float>::min()
+  T max_score = refine_min_score<T>();
   for (int d = dil_max; d > 0; --d) {
     const int rd = radius * d;
     const int diam = 2 * rd + 1;
@@ -427,9 +437,9 @@ refine_f32_kernel(const float* __restrict__ D11, const float* __restrict__ D21,
       for (int j = 0; j < diam; j += d) {
         const long long u = u0 - rd + i, v = v0 - rd + j;
         if (v >= 0 && v < H && u >= 0 && u < W) {
-          const float* row = img + ((size_t)v * W + (size_t)u) * F;
-          float s = 0.0f;
-          for (int k = 0; k < F; ++k) s = __fmaf_rn(__ldg(q + k), __ldg(row + k), s);
+          const T* row = img + ((size_t)v * W + (size_t)u) * F;
+          T s = (T)0;
+          for (int k = 0; k < F; ++k) s = fma(__ldg(q + k), __ldg(row + k), s);
           if (s > max_score) {
             max_score = s;
             u_new = u;
@@ -541,7 +551,19 @@ int launch_refine_f32(const float* D11, const float* D21, const int64_t* p1, int
                       cudaStream_t s) {
   if (B == 0 || N == 0) return FRODO_OK;
   dim3 grid((N + 127) / 128, B);
-  refine_f32_kernel<<<grid, 128, 0, s>>>(D11, D21, p1, p1_new, scores, H, W, N, F, radius, dil);
+  refine_f32_kernel<float><<<grid, 128, 0, s>>>(D11, D21, p1, p1_new, scores, H, W, N, F, radius,
+                                                dil);
+  FRODO_CUDA_TRY(cudaGetLastError());
+  return FRODO_OK;
+}
+
+int launch_refine_f64(const double* D11, const double* D21, const int64_t* p1, int64_t* p1_new,
+                      double* scores, int B, int H, int W, int N, int F, int radius, int dil,
+                      cudaStream_t s) {
+  if (B == 0 || N == 0) return FRODO_OK;
+  dim3 grid((N + 127) / 128, B);
+  refine_f32_kernel<double><<<grid, 128, 0, s>>>(D11, D21, p1, p1_new, scores, H, W, N, F, radius,
+                                                 dil);
   FRODO_CUDA_TRY(cudaGetLastError());
   return FRODO_OK;
 }

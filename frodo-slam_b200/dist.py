@@ -34,7 +34,7 @@ def _peer_state(numel, dev, group):
     FRODO_PEER_REDUCE=0 forces NCCL."""
     if os.environ.get("FRODO_PEER_REDUCE", "1") == "0" or dev.type != "cuda":
         return None
-    key = (id(group), dev.index, numel)
+    key = (_group_key(group), dev.index, numel)
     if key in _PEER_CACHE:
         return _PEER_CACHE[key]
     st = None

@@ -256,7 +256,10 @@ class KeyframeGraphArena:
         place.  mode / params as ``backends.make_params`` ("rays": sigma_ray, sigma_dist,
         C_thresh, Q_thresh; "points": sigma_point, ...; "calib": + height, width,
         pixel_border, z_eps and K [3,3]).  Returns (dx [Ku - num_fix, 7], unique keyframe ids):
-        the same dx the drop-in operator returns for the stacked inputs."""
+        the same dx the drop-in operator returns for the stacked inputs.  With odometry terms
+        (``odom``) that equality needs keyframe id == row of the stacked ``Twc`` (ids 0..K-1 in
+        order): the drop-in op and the reference index ``Twc`` by the RAW odometry ids
+        (gn_kernels.cu:1121-1122) while the arena looks the ids up in its slots."""
         if not self._ii:
             raise RuntimeError("no edges in the arena")
         prm = make_params(mode, **params)

@@ -57,7 +57,8 @@ int frodo_iter_proj(const float* rays_img, const float* pts_3d_norm, const float
                     float lambda_init, float cost_thresh, frodo_stream_t stream);
 
 /* ---- refine_matches: matching_kernels.cu:25-125 ---------------------------
- * D11 [B,H,W,F], D21 [B,N,F] (IEEE fp16 for _f16, fp32 for _f32), p1 [B,N,2]
+ * D11 [B,H,W,F], D21 [B,N,F] (IEEE fp16 for _f16, fp32 for _f32, fp64 for _f64: the three
+ * dispatch cases of the reference, matching_kernels.cu:112), p1 [B,N,2]
  * i64 (u,v).  Outputs p1_new [B,N,2] i64, max_scores [B,N] (same dtype as D).
  * fp16 path rounds to fp16 after every multiply and every add (c10::Half). */
 int frodo_refine_matches_f16(const void* D11, const void* D21, const int64_t* p1, int64_t* p1_new,
@@ -66,6 +67,9 @@ int frodo_refine_matches_f16(const void* D11, const void* D21, const int64_t* p1
 int frodo_refine_matches_f32(const float* D11, const float* D21, const int64_t* p1,
                              int64_t* p1_new, float* max_scores, int B, int H, int W, int N, int F,
                              int radius, int dilation_max, frodo_stream_t stream);
+int frodo_refine_matches_f64(const double* D11, const double* D21, const int64_t* p1,
+                             int64_t* p1_new, double* max_scores, int B, int H, int W, int N,
+                             int F, int radius, int dilation_max, frodo_stream_t stream);
 /* Tuning / test switch of the tile-staged fp16 kernel: query-patch edge 16 or 32, 0 = automatic
  * (16 for F <= 24).  Both variants are bit-identical; returns the value now in force.  The
  * environment variable FRODO_REFINE_PATCH seeds it once per process. */

@@ -101,6 +101,35 @@ def test_refine_matches_bit_exact_vs_oracle(be, dev, B, H, W, F, dtype):
     assert np.array_equal(sc.cpu().numpy().view(w), sr.view(w))
 
 
+def test_refine_matches_float64(be, dev):
+    """The reference dispatches double as well (matching_kernels.cu:112): same indices as a
+    float64 brute force in torch (fma order as the kernel: k ascending)."""
+    D11, D21, p1 = _refine_inputs(1, 24, 32, 19, torch.float64)
+    pn, sc = be.refine_matches(D11.to(dev), D21.to(dev), p1.to(dev), 2, 2)
+    assert sc.dtype == torch.float64 and pn.dtype == torch.int64
+    H, W = 24, 32
+    q = D21[0]
+    best = torch.full((H * W,), 2.2250738585072014e-308, dtype=torch.float64)
+    u0, v0 = p1[0, :, 0].clone(), p1[0, :, 1].clone()
+    bu, bv = u0.clone(), v0.clone()
+    img = D11[0].reshape(H * W, -1)
+    for d in (2, 1):
+        rd = 2 * d
+        for i in range(0, 2 * rd + 1, d):
+            for j in range(0, 2 * rd + 1, d):
+                u, v = u0 - rd + i, v0 - rd + j
+                inside = (v >= 0) & (v < H) & (u >= 0) & (u < W)
+                c = img[v.clamp(0, H - 1) * W + u.clamp(0, W - 1)]
+                s = (q * c).sum(1)
+                better = inside & (s > best + 1e-12)
+                best = torch.where(better, s, best)
+                bu, bv = torch.where(better, u, bu), torch.where(better, v, bv)
+        u0, v0 = bu.clone(), bv.clone()
+    same = (pn[0, :, 0].cpu() == bu) & (pn[0, :, 1].cpu() == bv)
+    assert same.float().mean() > 0.995  # ties at the 1e-12 level may resolve differently
+    assert torch.allclose(sc[0].cpu()[same], best[same], rtol=1e-10, atol=1e-300)
+
+
 @pytest.mark.parametrize("radius,dil", [(1, 1), (2, 3), (3, 5), (0, 2)])
 def test_refine_matches_search_shapes(be, dev, radius, dil):
     from oracle import oracle
