@@ -55,6 +55,89 @@ __device__ __forceinline__ Weights bilinear_weights(float u, float v) {
   return w;
 }
 
+// Levenberg-Marquardt state of one query pixel.  Consecutive iterations of the reference
+// (matching_kernels.cu:162-279) recompute identical quantities: after an ACCEPTED step the next
+// iteration blends the ray at exactly the trial position (same weights, same texels), so its
+// ray, norm, error and cost are bit-for-bit the trial's; after a REJECTED step the position does
+// not move and only lambda changes.  The state therefore carries the evaluation at (u, v) --
+// error, cost, the blended d(ray_x)/dx that shares its texel quad-word with the ray -- and the
+// five gradient sums, which are refreshed only after the position moved.  Same operations on the
+// same inputs as the reference, so the results stay bit-identical; per iteration one 4-channel
+// and (after a move) one 5-channel bilinear fetch instead of 9 + 3 channels, one sqrt/rcp pair
+// instead of two.
+struct Lm {
+  float u, v, lambda;
+  bool conv;
+  Weights w;              // bilinear footprint at (u, v)
+  float e0, e1, e2, cost; // ray error at (u, v)
+  float gx0;              // blended channel 3 at (u, v)
+  float A00, A01, A11, egx, egy;  // gradient sums at (u, v), without lambda
+  bool have_grad;
+};
+
+// fetch(w, c0, c1, out): out[j - c0] = blended channel j, c0 <= j < c1, at the footprint w.
+template <typename Fetch>
+__device__ __forceinline__ void lm_begin(Lm& s, float tx, float ty, float tz, Fetch&& fetch) {
+  s.w = bilinear_weights(s.u, s.v);
+  float c[4];
+  fetch(s.w, 0, 4, c);
+  const float nrm = __fsqrt_rn(sum3(c[0], c[1], c[2], c[0], c[1], c[2]));
+  const float inv = __frcp_rn(nrm);
+  s.e0 = __fmaf_rn(c[0], inv, -tx);
+  s.e1 = __fmaf_rn(c[1], inv, -ty);
+  s.e2 = __fmaf_rn(c[2], inv, -tz);
+  s.cost = sum3(s.e0, s.e1, s.e2, s.e0, s.e1, s.e2);
+  s.gx0 = c[3];
+  s.have_grad = false;
+}
+
+template <typename Fetch>
+__device__ __forceinline__ void lm_iteration(Lm& s, float tx, float ty, float tz, float umax,
+                                             float vmax, float cost_thresh, Fetch&& fetch) {
+  if (!s.have_grad) {
+    float g[5];  // gx1, gx2, gy0, gy1, gy2
+    fetch(s.w, 4, 9, g);
+    s.A00 = sum3(s.gx0, g[0], g[1], s.gx0, g[0], g[1]);
+    s.A01 = sum3(s.gx0, g[0], g[1], g[2], g[3], g[4]);
+    s.A11 = sum3(g[2], g[3], g[4], g[2], g[3], g[4]);
+    s.egx = sum3(s.e0, s.e1, s.e2, s.gx0, g[0], g[1]);
+    s.egy = sum3(s.e0, s.e1, s.e2, g[2], g[3], g[4]);
+    s.have_grad = true;
+  }
+  const float A00 = __fadd_rn(s.A00, s.lambda);
+  const float A11 = __fadd_rn(s.A11, s.lambda);
+  const float det = __fmaf_rn(A00, A11, -__fmul_rn(s.A01, s.A01));
+  const float det_inv = __frcp_rn(det);
+  const float num_u = __fmaf_rn(s.A01, s.egy, -__fmul_rn(s.egx, A11));
+  const float num_v = __fmaf_rn(s.A01, s.egx, -__fmul_rn(s.egy, A00));
+  const float u_new = clampf(__fmaf_rn(num_u, det_inv, s.u), 1.0f, umax);
+  const float v_new = clampf(__fmaf_rn(num_v, det_inv, s.v), 1.0f, vmax);
+
+  const Weights q = bilinear_weights(u_new, v_new);
+  float d[4];
+  fetch(q, 0, 4, d);
+  const float nrm2 = __fsqrt_rn(sum3(d[0], d[1], d[2], d[0], d[1], d[2]));
+  const float inv2 = __frcp_rn(nrm2);
+  const float f0 = __fmaf_rn(d[0], inv2, -tx);
+  const float f1 = __fmaf_rn(d[1], inv2, -ty);
+  const float f2 = __fmaf_rn(d[2], inv2, -tz);
+  const float new_cost = sum3(f0, f1, f2, f0, f1, f2);
+  if (new_cost < s.cost) {
+    s.u = u_new;
+    s.v = v_new;
+    s.w = q;
+    s.e0 = f0; s.e1 = f1; s.e2 = f2;
+    s.cost = new_cost;
+    s.gx0 = d[3];
+    s.have_grad = false;
+    s.lambda = __double2float_rn(__dmul_rn((double)s.lambda, 0.1));
+    s.conv = new_cost < cost_thresh;
+  } else {
+    s.lambda = __fmul_rn(s.lambda, 10.0f);
+    s.conv = s.cost < cost_thresh;
+  }
+}
+
 // One thread per query pixel; texels fetched through L1 (read-only path).
 __global__ void __launch_bounds__(128)
 iter_proj_kernel(const float* __restrict__ rays, const float* __restrict__ pts,
@@ -72,71 +155,25 @@ iter_proj_kernel(const float* __restrict__ rays, const float* __restrict__ pts,
   const float tz = __ldg(pts + t * 3 + 2);
   const float2 p0 = __ldg(reinterpret_cast<const float2*>(p_init) + t);
   const float umax = (float)(W - 2), vmax = (float)(H - 2);
-  float u = clampf(p0.x, 1.0f, umax);
-  float v = clampf(p0.y, 1.0f, vmax);
-  float lambda = lambda_init;
-  bool conv = false;
-
-  for (int it = 0; it < max_iter; ++it) {
-    const Weights w = bilinear_weights(u, v);
-    const float* r22 = img + ((size_t)w.v11 * W + w.u11) * 9;  // (v11,   u11)
-    const float* r21 = r22 + 9;                                 // (v11,   u11+1)
-    const float* r12 = r22 + (size_t)W * 9;                     // (v11+1, u11)
-    const float* r11 = r12 + 9;                                 // (v11+1, u11+1)
-    float c[9];
+  Lm s;
+  s.u = clampf(p0.x, 1.0f, umax);
+  s.v = clampf(p0.y, 1.0f, vmax);
+  s.lambda = lambda_init;
+  s.conv = false;
+  auto fetch_global = [&](const Weights& w, int c0, int c1, float* out) {
+    const float* r22 = img + ((size_t)w.v11 * W + w.u11) * 9;  // (v11, u11); +9: u11+1; +9W: v11+1
+    const float* r12 = r22 + (size_t)W * 9;
 #pragma unroll
     for (int j = 0; j < 9; ++j)
-      c[j] = blend(w.w11, __ldg(r11 + j), w.w12, __ldg(r12 + j), w.w21, __ldg(r21 + j), w.w22,
-                   __ldg(r22 + j));
-    const float nrm = __fsqrt_rn(sum3(c[0], c[1], c[2], c[0], c[1], c[2]));
-    const float inv = __frcp_rn(nrm);
-    const float e0 = __fmaf_rn(c[0], inv, -tx);
-    const float e1 = __fmaf_rn(c[1], inv, -ty);
-    const float e2 = __fmaf_rn(c[2], inv, -tz);
-    const float cost = sum3(e0, e1, e2, e0, e1, e2);
-    float A00 = sum3(c[3], c[4], c[5], c[3], c[4], c[5]);
-    const float A01 = sum3(c[3], c[4], c[5], c[6], c[7], c[8]);
-    float A11 = sum3(c[6], c[7], c[8], c[6], c[7], c[8]);
-    const float egx = sum3(e0, e1, e2, c[3], c[4], c[5]);
-    const float egy = sum3(e0, e1, e2, c[6], c[7], c[8]);
-    A00 = __fadd_rn(A00, lambda);
-    A11 = __fadd_rn(A11, lambda);
-    const float det = __fmaf_rn(A00, A11, -__fmul_rn(A01, A01));
-    const float det_inv = __frcp_rn(det);
-    const float num_u = __fmaf_rn(A01, egy, -__fmul_rn(egx, A11));
-    const float num_v = __fmaf_rn(A01, egx, -__fmul_rn(egy, A00));
-    const float u_new = clampf(__fmaf_rn(num_u, det_inv, u), 1.0f, umax);
-    const float v_new = clampf(__fmaf_rn(num_v, det_inv, v), 1.0f, vmax);
-
-    const Weights q = bilinear_weights(u_new, v_new);
-    const float* s22 = img + ((size_t)q.v11 * W + q.u11) * 9;
-    const float* s21 = s22 + 9;
-    const float* s12 = s22 + (size_t)W * 9;
-    const float* s11 = s12 + 9;
-    float d[3];
-#pragma unroll
-    for (int j = 0; j < 3; ++j)
-      d[j] = blend(q.w11, __ldg(s11 + j), q.w12, __ldg(s12 + j), q.w21, __ldg(s21 + j), q.w22,
-                   __ldg(s22 + j));
-    const float nrm2 = __fsqrt_rn(sum3(d[0], d[1], d[2], d[0], d[1], d[2]));
-    const float inv2 = __frcp_rn(nrm2);
-    const float f0 = __fmaf_rn(d[0], inv2, -tx);
-    const float f1 = __fmaf_rn(d[1], inv2, -ty);
-    const float f2 = __fmaf_rn(d[2], inv2, -tz);
-    const float new_cost = sum3(f0, f1, f2, f0, f1, f2);
-
-    if (new_cost < cost) {
-      u = u_new;
-      v = v_new;
-      lambda = __double2float_rn(__dmul_rn((double)lambda, 0.1));
-      conv = new_cost < cost_thresh;
-    } else {
-      lambda = __fmul_rn(lambda, 10.0f);
-      conv = cost < cost_thresh;
-    }
-  }
-  reinterpret_cast<float2*>(p_new)[t] = make_float2(u, v);
-  converged[t] = conv ? 1 : 0;
+      if (j >= c0 && j < c1)
+        out[j - c0] = blend(w.w11, __ldg(r12 + 9 + j), w.w12, __ldg(r12 + j), w.w21,
+                            __ldg(r22 + 9 + j), w.w22, __ldg(r22 + j));
+  };
+  if (max_iter > 0) lm_begin(s, tx, ty, tz, fetch_global);
+  for (int it = 0; it < max_iter; ++it)
+    lm_iteration(s, tx, ty, tz, umax, vmax, cost_thresh, fetch_global);
+  reinterpret_cast<float2*>(p_new)[t] = make_float2(s.u, s.v);
+  converged[t] = s.conv ? 1 : 0;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -153,59 +190,6 @@ iter_proj_kernel(const float* __restrict__ rays, const float* __restrict__ pts,
 constexpr int kWinPatchW = 32, kWinPatchH = 16, kWinThreads = kWinPatchW * kWinPatchH;
 constexpr int kWinMargin = 4;
 constexpr int kWinSmemBytes = 108 * 1024;  // 2 CTAs per SM
-
-struct Lm {
-  float u, v, lambda;
-  bool conv;
-};
-
-// One LM iteration; texel(j, corner) returns channel j of corner 0..3 = (v11,u11), (v11,u11+1),
-// (v11+1,u11), (v11+1,u11+1) of the footprint selected by the last call of `locate`.
-template <typename Fetch>
-__device__ __forceinline__ void lm_iteration(Lm& s, float tx, float ty, float tz, float umax,
-                                             float vmax, float cost_thresh, Fetch&& fetch) {
-  const Weights w = bilinear_weights(s.u, s.v);
-  float c[9];
-  fetch(w.u11, w.v11, c, 9, w);
-  const float nrm = __fsqrt_rn(sum3(c[0], c[1], c[2], c[0], c[1], c[2]));
-  const float inv = __frcp_rn(nrm);
-  const float e0 = __fmaf_rn(c[0], inv, -tx);
-  const float e1 = __fmaf_rn(c[1], inv, -ty);
-  const float e2 = __fmaf_rn(c[2], inv, -tz);
-  const float cost = sum3(e0, e1, e2, e0, e1, e2);
-  float A00 = sum3(c[3], c[4], c[5], c[3], c[4], c[5]);
-  const float A01 = sum3(c[3], c[4], c[5], c[6], c[7], c[8]);
-  float A11 = sum3(c[6], c[7], c[8], c[6], c[7], c[8]);
-  const float egx = sum3(e0, e1, e2, c[3], c[4], c[5]);
-  const float egy = sum3(e0, e1, e2, c[6], c[7], c[8]);
-  A00 = __fadd_rn(A00, s.lambda);
-  A11 = __fadd_rn(A11, s.lambda);
-  const float det = __fmaf_rn(A00, A11, -__fmul_rn(A01, A01));
-  const float det_inv = __frcp_rn(det);
-  const float num_u = __fmaf_rn(A01, egy, -__fmul_rn(egx, A11));
-  const float num_v = __fmaf_rn(A01, egx, -__fmul_rn(egy, A00));
-  const float u_new = clampf(__fmaf_rn(num_u, det_inv, s.u), 1.0f, umax);
-  const float v_new = clampf(__fmaf_rn(num_v, det_inv, s.v), 1.0f, vmax);
-
-  const Weights q = bilinear_weights(u_new, v_new);
-  float d[9];
-  fetch(q.u11, q.v11, d, 3, q);
-  const float nrm2 = __fsqrt_rn(sum3(d[0], d[1], d[2], d[0], d[1], d[2]));
-  const float inv2 = __frcp_rn(nrm2);
-  const float f0 = __fmaf_rn(d[0], inv2, -tx);
-  const float f1 = __fmaf_rn(d[1], inv2, -ty);
-  const float f2 = __fmaf_rn(d[2], inv2, -tz);
-  const float new_cost = sum3(f0, f1, f2, f0, f1, f2);
-  if (new_cost < cost) {
-    s.u = u_new;
-    s.v = v_new;
-    s.lambda = __double2float_rn(__dmul_rn((double)s.lambda, 0.1));
-    s.conv = new_cost < cost_thresh;
-  } else {
-    s.lambda = __fmul_rn(s.lambda, 10.0f);
-    s.conv = cost < cost_thresh;
-  }
-}
 
 __global__ void __launch_bounds__(kWinThreads, 2)
 iter_proj_window_kernel(const float* __restrict__ rays, const float* __restrict__ pts,
@@ -229,7 +213,10 @@ iter_proj_window_kernel(const float* __restrict__ rays, const float* __restrict_
   }
   float tx = 0.f, ty = 0.f, tz = 0.f;
   const float umax = (float)(W - 2), vmax = (float)(H - 2);
-  Lm s = {1.0f, 1.0f, lambda_init, false};
+  Lm s;
+  s.u = s.v = 1.0f;
+  s.lambda = lambda_init;
+  s.conv = false;
   if (active) {
     tx = __ldg(pts + t * 3 + 0);
     ty = __ldg(pts + t * 3 + 1);
@@ -238,16 +225,19 @@ iter_proj_window_kernel(const float* __restrict__ rays, const float* __restrict_
     s.u = clampf(p0.x, 1.0f, umax);
     s.v = clampf(p0.y, 1.0f, vmax);
   }
-  auto fetch_global = [&](int u11, int v11, float* c, int nch, const Weights& w) {
-    const float* r22 = img + ((size_t)v11 * W + u11) * 9;
+  auto fetch_global = [&](const Weights& w, int c0, int c1, float* out) {
+    const float* r22 = img + ((size_t)w.v11 * W + w.u11) * 9;
     const float* r12 = r22 + (size_t)W * 9;
 #pragma unroll
     for (int j = 0; j < 9; ++j)
-      if (j < nch)
-        c[j] = blend(w.w11, __ldg(r12 + 9 + j), w.w12, __ldg(r12 + j), w.w21, __ldg(r22 + 9 + j),
-                     w.w22, __ldg(r22 + j));
+      if (j >= c0 && j < c1)
+        out[j - c0] = blend(w.w11, __ldg(r12 + 9 + j), w.w12, __ldg(r12 + j), w.w21,
+                            __ldg(r22 + 9 + j), w.w22, __ldg(r22 + j));
   };
-  if (active && max_iter > 0) lm_iteration(s, tx, ty, tz, umax, vmax, cost_thresh, fetch_global);
+  if (active && max_iter > 0) {
+    lm_begin(s, tx, ty, tz, fetch_global);
+    lm_iteration(s, tx, ty, tz, umax, vmax, cost_thresh, fetch_global);
+  }
   __syncthreads();  // box / barrier initialised
   if (max_iter > 1) {
     int mnu = INT_MAX, mxu = INT_MIN, mnv = INT_MAX, mxv = INT_MIN;
@@ -295,17 +285,18 @@ iter_proj_window_kernel(const float* __restrict__ rays, const float* __restrict_
     ptx::mbar_wait(&bar, 0);
   }
   if (active) {
-    auto fetch_window = [&](int u11, int v11, float* c, int nch, const Weights& w) {
-      const int ru = u11 - tu0, rv = v11 - tv0;
+    auto fetch_window = [&](const Weights& w, int c0, int c1, float* out) {
+      const int ru = w.u11 - tu0, rv = w.v11 - tv0;
       if (ru >= 0 && ru + 1 < TW && rv >= 0 && rv + 1 < TH) {
         const float* r22 = win + (rv * TW + ru) * 9;
         const float* r12 = r22 + TW * 9;
 #pragma unroll
         for (int j = 0; j < 9; ++j)
-          if (j < nch)
-            c[j] = blend(w.w11, r12[9 + j], w.w12, r12[j], w.w21, r22[9 + j], w.w22, r22[j]);
+          if (j >= c0 && j < c1)
+            out[j - c0] = blend(w.w11, r12[9 + j], w.w12, r12[j], w.w21, r22[9 + j], w.w22,
+                                r22[j]);
       } else {
-        fetch_global(u11, v11, c, nch, w);
+        fetch_global(w, c0, c1, out);
       }
     };
     for (int it = 1; it < max_iter; ++it)
