@@ -226,7 +226,7 @@ def run_matching(device, B, steps, warmup, peak, be=None, hw=None):
 
 def run_match_pipeline(device, B, steps, warmup, peak):
     """px-matches/s through the drop-in ``match()`` (mast3r_slam/matching.py:8-10: prologue,
-    iter_proj, occlusion test, fp16 cast, refine_matches, epilogue; one C-ABI call, six
+    iter_proj, occlusion test, fp16 cast, refine_matches, epilogue; one C-ABI call, four
     kernels), fp32 inputs resident in HBM, plus each HBM-bound glue kernel timed alone against
     its algorithmic bytes."""
     import ctypes
@@ -281,7 +281,9 @@ def run_match_pipeline(device, B, steps, warmup, peak):
     return {"metric": "px-matches/s through match() (matching.py:8-10), fp32 inputs in HBM",
             "value": px * steps / (ms * 1e-3), "unit": "px/s", "pairs": B, "resolution": "512x384",
             "ms_per_step": ms / steps, "glue_share_of_call": glue_ms / (ms / steps),
-            "glue_kernels": glue, "gpu_launches": 6 * steps}
+            "glue_kernels": glue, "gpu_launches": 4 * steps,
+            "kernels_per_call": "prep, iter_proj (+ occlusion test in its epilogue), fp16 cast of "
+                                "D11, refine_matches (+ threshold and linearisation in its epilogue)"}
 
 
 def cpu_baseline_gn(g_np, seconds=12.0):

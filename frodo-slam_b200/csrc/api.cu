@@ -221,18 +221,26 @@ int frodo_match(const frodo_match_params* prm, const float* X11, const float* X2
   const size_t nd = (size_t)B * N * F;
   int rc;
   if ((rc = launch_match_prep(X11, X21, idx_1_to_2_init, rays, pts, p_init, B, H, W, s))) return rc;
+  // iter_proj with the occlusion test (matching.py:66-75) in its epilogue: p_iter / converged are
+  // never written, p1 and the first validity mask come straight from the registers
+  const IterProjTail itail = {X11, X21, prm->dist_thresh, p1, v0};
   if ((rc = launch_iter_proj(rays, pts, p_init, p_iter, conv, B, H, W, N, prm->max_iter,
-                             prm->lambda_init, prm->convergence_thresh, s)))
-    return rc;
-  if ((rc = launch_match_occlusion(X11, X21, p_iter, conv, prm->dist_thresh, p1, v0, B, H, W, s)))
+                             prm->lambda_init, prm->convergence_thresh, s, &itail)))
     return rc;
   if ((rc = launch_convert_f32_f16(D11, d11h, nd, s))) return rc;
   // the tile-staged refine kernel converts the query descriptors while loading them
   // (matching.py:80 fused): the cast pass over D21 and its fp16 copy are only needed otherwise
   const bool fuse_d21 = refine_f16_takes_tile_kernel(d11h, D21, p1, p1_new, B, H, W, N, F);
   if (!fuse_d21 && (rc = launch_convert_f32_f16(D21, d21h, nd, s))) return rc;
+  if (fuse_d21) {
+    // ... and the threshold + linearisation (matching.py:87-92) in refine_matches' epilogue:
+    // four kernels per call (prep, iter_proj, cast of D11, refine_matches)
+    const RefineTail rtail = {v0, prm->ft_matching_threshold, idx_1_to_2, valid};
+    return launch_refine_f16(d11h, d21h, p1, p1_new, scores, B, H, W, N, F, prm->radius,
+                             prm->dilation_max, s, D21, &rtail);
+  }
   if ((rc = launch_refine_f16(d11h, d21h, p1, p1_new, scores, B, H, W, N, F, prm->radius,
-                              prm->dilation_max, s, fuse_d21 ? D21 : nullptr)))
+                              prm->dilation_max, s, nullptr)))
     return rc;
   return launch_match_finish(p1_new, scores, true, v0, prm->ft_matching_threshold, idx_1_to_2,
                              valid, B, N, W, s);

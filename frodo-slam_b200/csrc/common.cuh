@@ -53,13 +53,31 @@ int cuda_fail(cudaError_t e, const char* what);
     }                                                                   \
   } while (0)
 
+// Fused tails of the matching pipeline (frodo_match, matching.py:66-92): when set, the kernel
+// writes the NEXT stage's outputs from its epilogue instead of its own.
+struct IterProjTail {   // matching.py:66-75: p1 = trunc(p), valid = converged & |X11[p1] - X21| < thresh
+  const float* X11;     // [B,H,W,3]; NULL = no tail (write p_new, converged)
+  const float* X21;     // [B,H*W,3]
+  float dist_thresh;
+  int64_t* p1;          // [B,H*W,2]
+  uint8_t* valid;       // [B,H*W]
+};
+struct RefineTail {     // matching.py:87-92: valid &= score > threshold (fp16 compare), idx = x + W y
+  const uint8_t* valid_in;  // NULL = no tail (write p1_new, scores)
+  float threshold;
+  int64_t* idx;         // [B,N]
+  uint8_t* valid;       // [B,N]
+};
+
 // Launchers implemented in the .cu files (host side, return FRODO_* codes).
 int launch_iter_proj(const float* rays, const float* pts, const float* p_init, float* p_new,
                      uint8_t* converged, int B, int H, int W, int N, int max_iter,
-                     float lambda_init, float cost_thresh, cudaStream_t s);
+                     float lambda_init, float cost_thresh, cudaStream_t s,
+                     const IterProjTail* tail = nullptr);
 int launch_refine_f16(const __half* D11, const __half* D21, const int64_t* p1, int64_t* p1_new,
                       __half* scores, int B, int H, int W, int N, int F, int radius, int dil,
-                      cudaStream_t s, const float* D21_f32 = nullptr);
+                      cudaStream_t s, const float* D21_f32 = nullptr,
+                      const RefineTail* tail = nullptr);
 int refine_forced_patch(int set);
 bool refine_f16_takes_tile_kernel(const void* D11, const void* D21, const void* p1,
                                   const void* p1_new, int B, int H, int W, int N, int F);

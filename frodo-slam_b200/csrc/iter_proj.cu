@@ -138,12 +138,36 @@ __device__ __forceinline__ void lm_iteration(Lm& s, float tx, float ty, float tz
   }
 }
 
+// Result of one query pixel: the op's own outputs, or (frodo_match) the occlusion test of
+// matching.py:66-75 straight from the registers -- p1 = trunc(p), valid = converged &
+// (||X11[p1] - X21|| < dist_thresh), arithmetic as match_occlusion_kernel (match_glue.cu).
+__device__ __forceinline__ void store_result(const Lm& s, size_t t, size_t b, int H, int W,
+                                             float* __restrict__ p_new,
+                                             uint8_t* __restrict__ converged,
+                                             const IterProjTail& tail) {
+  if (tail.X11 == nullptr) {
+    reinterpret_cast<float2*>(p_new)[t] = make_float2(s.u, s.v);
+    converged[t] = s.conv ? 1 : 0;
+    return;
+  }
+  const long long px = (long long)s.u, py = (long long)s.v;  // .long(): toward zero
+  reinterpret_cast<longlong2*>(tail.p1)[t] = make_longlong2(px, py);
+  const long long gx = min(max(px, 0LL), (long long)W - 1), gy = min(max(py, 0LL), (long long)H - 1);
+  const float* a = tail.X11 + (b * (size_t)H * W + (size_t)gy * W + (size_t)gx) * 3;
+  const float* q = tail.X21 + t * 3;
+  const float d0 = __fsub_rn(__ldg(a), __ldg(q));
+  const float d1 = __fsub_rn(__ldg(a + 1), __ldg(q + 1));
+  const float d2 = __fsub_rn(__ldg(a + 2), __ldg(q + 2));
+  const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(d0, d0), __fmul_rn(d1, d1)), __fmul_rn(d2, d2));
+  tail.valid[t] = s.conv && (__fsqrt_rn(n2) < tail.dist_thresh);
+}
+
 // One thread per query pixel; texels fetched through L1 (read-only path).
 __global__ void __launch_bounds__(128)
 iter_proj_kernel(const float* __restrict__ rays, const float* __restrict__ pts,
                  const float* __restrict__ p_init, float* __restrict__ p_new,
                  uint8_t* __restrict__ converged, int H, int W, int N, int max_iter,
-                 float lambda_init, float cost_thresh) {
+                 float lambda_init, float cost_thresh, const IterProjTail tail) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   const size_t b = blockIdx.y;
@@ -172,8 +196,7 @@ iter_proj_kernel(const float* __restrict__ rays, const float* __restrict__ pts,
   if (max_iter > 0) lm_begin(s, tx, ty, tz, fetch_global);
   for (int it = 0; it < max_iter; ++it)
     lm_iteration(s, tx, ty, tz, umax, vmax, cost_thresh, fetch_global);
-  reinterpret_cast<float2*>(p_new)[t] = make_float2(s.u, s.v);
-  converged[t] = s.conv ? 1 : 0;
+  store_result(s, t, b, H, W, p_new, converged, tail);  // the tail needs N == H * W
 }
 
 // ---------------------------------------------------------------------------------------
@@ -195,7 +218,7 @@ __global__ void __launch_bounds__(kWinThreads, 2)
 iter_proj_window_kernel(const float* __restrict__ rays, const float* __restrict__ pts,
                         const float* __restrict__ p_init, float* __restrict__ p_new,
                         uint8_t* __restrict__ converged, int H, int W, int max_iter,
-                        float lambda_init, float cost_thresh) {
+                        float lambda_init, float cost_thresh, const IterProjTail tail) {
   extern __shared__ __align__(128) float win[];
   __shared__ uint64_t bar;
   __shared__ int box[4];
@@ -301,8 +324,7 @@ iter_proj_window_kernel(const float* __restrict__ rays, const float* __restrict_
     };
     for (int it = 1; it < max_iter; ++it)
       lm_iteration(s, tx, ty, tz, umax, vmax, cost_thresh, fetch_window);
-    reinterpret_cast<float2*>(p_new)[t] = make_float2(s.u, s.v);
-    converged[t] = s.conv ? 1 : 0;
+    store_result(s, t, b, H, W, p_new, converged, tail);
   }
 }
 
@@ -310,8 +332,17 @@ iter_proj_window_kernel(const float* __restrict__ rays, const float* __restrict_
 
 int launch_iter_proj(const float* rays, const float* pts, const float* p_init, float* p_new,
                      uint8_t* converged, int B, int H, int W, int N, int max_iter,
-                     float lambda_init, float cost_thresh, cudaStream_t s) {
+                     float lambda_init, float cost_thresh, cudaStream_t s,
+                     const IterProjTail* tail_in) {
   if (B == 0 || N == 0) return FRODO_OK;
+  IterProjTail tail = {};
+  if (tail_in != nullptr) {
+    tail = *tail_in;
+    if (N != H * W) {
+      set_error("iter_proj: the occlusion tail needs N == H * W");
+      return FRODO_ERR_ARG;
+    }
+  }
   const bool aligned = (reinterpret_cast<uintptr_t>(rays) & 15) == 0 &&
                        (reinterpret_cast<uintptr_t>(p_init) & 7) == 0 &&
                        (reinterpret_cast<uintptr_t>(p_new) & 7) == 0;
@@ -326,13 +357,13 @@ int launch_iter_proj(const float* rays, const float* pts, const float* p_init, f
     }
     dim3 wgrid((W + kWinPatchW - 1) / kWinPatchW, (H + kWinPatchH - 1) / kWinPatchH, B);
     iter_proj_window_kernel<<<wgrid, kWinThreads, kWinSmemBytes, s>>>(
-        rays, pts, p_init, p_new, converged, H, W, max_iter, lambda_init, cost_thresh);
+        rays, pts, p_init, p_new, converged, H, W, max_iter, lambda_init, cost_thresh, tail);
     FRODO_CUDA_TRY(cudaGetLastError());
     return FRODO_OK;
   }
   dim3 grid((N + 127) / 128, B);
   iter_proj_kernel<<<grid, 128, 0, s>>>(rays, pts, p_init, p_new, converged, H, W, N, max_iter,
-                                        lambda_init, cost_thresh);
+                                        lambda_init, cost_thresh, tail);
   FRODO_CUDA_TRY(cudaGetLastError());
   return FRODO_OK;
 }

@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(PW * PH, (PW * PH >= 1024) ? 1 : 2)
 refine_f16_tile_kernel(const __half* __restrict__ D11, const __half* __restrict__ D21,
                        const int64_t* __restrict__ p1, int64_t* __restrict__ p1_new,
                        __half* __restrict__ scores, int H, int W, int radius, int dil_max,
-                       int cap_px, const float* __restrict__ D21_f32) {
+                       int cap_px, const float* __restrict__ D21_f32, const RefineTail tail) {
   extern __shared__ __align__(128) unsigned char tile[];
   __shared__ uint64_t bar;
   __shared__ int box[4];  // min u, max u, min v, max v of the centres that can reach the image
@@ -358,9 +358,16 @@ refine_f16_tile_kernel(const __half* __restrict__ D11, const __half* __restrict_
     }
   }
   if (active) {
-    reinterpret_cast<longlong2*>(p1_new)[t] =
-        reach ? make_longlong2((long long)u0, (long long)v0) : p;
-    scores[t] = max_score;
+    const longlong2 best = reach ? make_longlong2((long long)u0, (long long)v0) : p;
+    if (tail.valid_in == nullptr) {
+      reinterpret_cast<longlong2*>(p1_new)[t] = best;
+      scores[t] = max_score;
+    } else {
+      // frodo_match: matching.py:87-92 from the registers (as match_finish_kernel): the score is
+      // compared in fp16 against the threshold cast to fp16
+      tail.idx[t] = best.x + (long long)W * best.y;
+      tail.valid[t] = (tail.valid_in[t] != 0) && __hgt(max_score, __float2half_rn(tail.threshold));
+    }
   }
 }
 
@@ -482,7 +489,7 @@ int refine_forced_patch(int set) {
 
 int launch_refine_f16(const __half* D11, const __half* D21, const int64_t* p1, int64_t* p1_new,
                       __half* scores, int B, int H, int W, int N, int F, int radius, int dil,
-                      cudaStream_t s, const float* D21_f32) {
+                      cudaStream_t s, const float* D21_f32, const RefineTail* tail_in) {
   if (B == 0 || N == 0) return FRODO_OK;
   dim3 grid((N + 127) / 128, B);
   const bool aligned = ((reinterpret_cast<uintptr_t>(D11) | reinterpret_cast<uintptr_t>(D21) |
@@ -490,8 +497,10 @@ int launch_refine_f16(const __half* D11, const __half* D21, const int64_t* p1, i
                         15) == 0;
   const bool tile = refine_f16_takes_tile_kernel(D11, D21_f32 ? (const void*)D21_f32 : (const void*)D21,
                                                  p1, p1_new, B, H, W, N, F);
-  if (D21_f32 != nullptr && !tile) {
-    set_error("refine_matches: fp32 query descriptors need the tile-staged kernel");
+  RefineTail tail = {};
+  if (tail_in != nullptr) tail = *tail_in;
+  if ((D21_f32 != nullptr || tail.valid_in != nullptr) && !tile) {
+    set_error("refine_matches: fp32 query descriptors / the fused tail need the tile-staged kernel");
     return FRODO_ERR_ARG;
   }
   if (tile) {
@@ -517,7 +526,7 @@ int launch_refine_f16(const __half* D11, const __half* D21, const int64_t* p1, i
       once.mark(dev_);                                                                          \
     }                                                                                           \
     refine_f16_tile_kernel<FF, RR, PWW, PHH><<<tgrid, PWW * PHH, smem_bytes, s>>>(              \
-        D11, D21, p1, p1_new, scores, H, W, radius, dil, cap_px, D21_f32);                      \
+        D11, D21, p1, p1_new, scores, H, W, radius, dil, cap_px, D21_f32, tail);                \
   } while (0)
 #define FRODO_TILE_LAUNCH(FF, RR)                                                               \
   do {                                                                                          \
