@@ -64,6 +64,8 @@ SIGNATURES = {
     "frodo_match_occlusion": (c_int, [c_void_p] * 4 + [c_float, c_void_p, c_void_p] + [c_int] * 3 +
                               [c_void_p]),
     "frodo_convert_f32_f16": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
+    "frodo_constrain_points_to_ray": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p,
+                                              c_void_p]),
     "frodo_match_finish": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_float, c_void_p,
                                    c_void_p] + [c_int] * 3 + [c_void_p]),
     "frodo_match_workspace_bytes": (c_size_t, [c_int] * 4),

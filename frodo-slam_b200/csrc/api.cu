@@ -148,6 +148,14 @@ int frodo_convert_f32_f16(const float* src, void* dst, size_t n, frodo_stream_t 
                                 static_cast<cudaStream_t>(stream));
 }
 
+int frodo_constrain_points_to_ray(const float* Xs, const float* Kmat, int num_frames, int H, int W,
+                                  float* Xs_out, frodo_stream_t stream) {
+  FRODO_ARG_CHECK(num_frames >= 0 && H >= 1 && W >= 1);
+  FRODO_ARG_CHECK(num_frames == 0 || (Xs && Kmat && Xs_out));
+  return launch_constrain_points(Xs, Kmat, num_frames, H, W, Xs_out,
+                                 static_cast<cudaStream_t>(stream));
+}
+
 int frodo_match_finish(const int64_t* p1, const void* scores, int scores_f16,
                        const uint8_t* valid_in, float threshold, int64_t* idx_1_to_2,
                        uint8_t* valid, int B, int N, int W, frodo_stream_t stream) {

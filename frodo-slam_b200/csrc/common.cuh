@@ -96,6 +96,8 @@ int launch_match_occlusion(const float* X11, const float* X21, const float* p_it
                            const uint8_t* conv, float dist_thresh, int64_t* p1, uint8_t* valid,
                            int B, int H, int W, cudaStream_t s);
 int launch_convert_f32_f16(const float* src, __half* dst, size_t n, cudaStream_t s);
+int launch_constrain_points(const float* X, const float* Kmat, int num_frames, int H, int W,
+                            float* out, cudaStream_t s);
 int launch_match_finish(const int64_t* p1, const void* scores, bool scores_f16,
                         const uint8_t* valid_in, float threshold, int64_t* idx, uint8_t* valid,
                         int B, int N, int W, cudaStream_t s);

@@ -20,7 +20,7 @@
 // Parity note: phi goes through acosf(0.5 (trace - 1)), which quantises angles below ~5e-4 rad;
 // one ulp in R_err moves phi by 3e-4 rad at an information of 1e6.  The chain quaternion -> R ->
 // R_err therefore uses explicit _rn intrinsics in the operation order nvcc gives the reference
-// (read from its SASS, restated in oracle/frodo_oracle.c); everything after Log() is
+// (read from its SASS; the CPU restatement used by the tests follows it too); everything after Log() is
 // well-conditioned and written in this file's own form.
 //   * odom_add_kernel: one CTA per lower 7x7 block of H (like assemble_kernel), visiting the
 //     odometry edges in order (deterministic fp64 sums), SparseBlock::update_lhs/rhs semantics

@@ -277,6 +277,36 @@ int launch_match_occlusion(const float* X11, const float* X21, const float* p_it
   return FRODO_OK;
 }
 
+// constrain_points_to_ray (geometry.py:37-42 + backproject :107-115), what solve_GN_calib does
+// to the pointmaps before gauss_newton_calib (global_opt.py:296-300): point n of a frame keeps
+// its depth z and moves onto the ray of its pixel, X = z * ((u - cx) / fx, (v - cy) / fy, 1),
+// u = n mod W, v = n / W.  IEEE subtract, divide, multiply: bit-identical to the torch ops.
+namespace {
+__global__ void __launch_bounds__(256)
+constrain_points_kernel(const float* __restrict__ X, const float* __restrict__ Kmat, int HW,
+                        int W, size_t total, float* __restrict__ out) {
+  const float fx = __ldg(Kmat + 0), fy = __ldg(Kmat + 4), cx = __ldg(Kmat + 2), cy = __ldg(Kmat + 5);
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t n = (size_t)blockIdx.x * blockDim.x + threadIdx.x; n < total; n += stride) {
+    const int pix = (int)(n % (size_t)HW);
+    const float u = (float)(pix % W), v = (float)(pix / W);
+    const float z = __ldg(X + n * 3 + 2);
+    out[n * 3 + 0] = __fmul_rn(z, __fdiv_rn(__fsub_rn(u, cx), fx));
+    out[n * 3 + 1] = __fmul_rn(z, __fdiv_rn(__fsub_rn(v, cy), fy));
+    out[n * 3 + 2] = __fmul_rn(z, 1.0f);
+  }
+}
+}  // namespace
+
+int launch_constrain_points(const float* X, const float* Kmat, int num_frames, int H, int W,
+                            float* out, cudaStream_t s) {
+  const size_t total = (size_t)num_frames * H * W;
+  if (total == 0) return FRODO_OK;
+  constrain_points_kernel<<<stream_blocks(total), 256, 0, s>>>(X, Kmat, H * W, W, total, out);
+  FRODO_CUDA_TRY(cudaGetLastError());
+  return FRODO_OK;
+}
+
 int launch_convert_f32_f16(const float* src, __half* dst, size_t n, cudaStream_t s) {
   if (n == 0) return FRODO_OK;
   convert_f32_f16_kernel<<<stream_blocks(n / 8 + 1), 256, 0, s>>>(src, dst, n);

@@ -39,6 +39,26 @@ def _ptr(t):
     return ctypes.c_void_p(t.data_ptr()) if t is not None and t.numel() > 0 else None
 
 
+def constrain_points_to_ray(img_size, Xs, K, out=None):
+    """mast3r_slam/geometry.py:37-42 (same name and argument order): every point keeps its depth
+    and moves onto the ray of its pixel.  Xs [..., H*W, 3] f32 CUDA, K [3,3] f32 CUDA; what
+    ``solve_GN_calib`` does before ``gauss_newton_calib`` (global_opt.py:296-300), one kernel."""
+    h, w = int(img_size[0]), int(img_size[1])
+    if not Xs.is_cuda or Xs.dtype != torch.float32 or not Xs.is_contiguous():
+        raise RuntimeError("Xs must be a contiguous float32 CUDA tensor")
+    if not K.is_cuda or K.dtype != torch.float32 or K.numel() != 9 or not K.is_contiguous():
+        raise RuntimeError("K must be a contiguous float32 [3,3] CUDA tensor")
+    if Xs.shape[-1] != 3 or Xs.numel() % (3 * h * w) != 0:
+        raise RuntimeError("Xs must be [..., H*W, 3] for the given img_size")
+    if out is None:
+        out = torch.empty_like(Xs)
+    with torch.cuda.device(Xs.device):
+        _lib.check(_lib.load().frodo_constrain_points_to_ray(
+            _ptr(Xs), _ptr(K), Xs.numel() // (3 * h * w), h, w, _ptr(out),
+            ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return out
+
+
 class KeyframeGraphArena:
     def __init__(self, num_points, max_keyframes, max_edges, device="cuda"):
         """num_points: N = H*W; max_keyframes: ring capacity (the sliding window of
@@ -78,10 +98,13 @@ class KeyframeGraphArena:
     def keyframe_ids(self):
         return sorted(k for k in self._kf_of_slot if k is not None)
 
-    def put_keyframe(self, kf_id, X, C, T_WC=None):
+    def put_keyframe(self, kf_id, X, C, T_WC=None, calib=None):
         """Add keyframe `kf_id`, or overwrite its pointmap / confidence (and pose, if given).
         X [N,3] (or [H,W,3]), C [N] (or [N,1]) f32 on the device.  The ring slot must be free
-        or already hold this id: evict first (``evict_older_than``)."""
+        or already hold this id: evict first (``evict_older_than``).  ``calib=(img_size, K)``:
+        the pointmap is re-projected onto its pixel rays as it is stored
+        (``constrain_points_to_ray``, what ``solve_GN_calib`` does per solve,
+        global_opt.py:296-300), so calibrated solves run on the arena directly."""
         kf_id = int(kf_id)
         s = kf_id % self.Kcap
         if self._kf_of_slot[s] is not None and self._kf_of_slot[s] != kf_id:
@@ -93,7 +116,11 @@ class KeyframeGraphArena:
         self._dev_f32(X, "X", self.N * 3)
         self._dev_f32(C, "C", self.N)
         with torch.cuda.device(self.dev):
-            self.Xs[s].copy_(X.reshape(self.N, 3))
+            if calib is not None:
+                constrain_points_to_ray(calib[0], X.reshape(self.N, 3).contiguous(), calib[1],
+                                        out=self.Xs[s])
+            else:
+                self.Xs[s].copy_(X.reshape(self.N, 3))
             self.Cs[s].copy_(C.reshape(self.N, 1))
             if T_WC is not None:
                 self.set_pose(kf_id, T_WC, _slot=s)

@@ -114,6 +114,13 @@ int frodo_match_occlusion(const float* X11, const float* X21, const float* p_ite
                           const uint8_t* converged, float dist_thresh, int64_t* p1, uint8_t* valid,
                           int B, int H, int W, frodo_stream_t stream);
 int frodo_convert_f32_f16(const float* src, void* dst, size_t n, frodo_stream_t stream);
+/* constrain_points_to_ray (mast3r_slam/geometry.py:37-42, :107-115), the re-projection
+ * solve_GN_calib applies to the pointmaps before gauss_newton_calib (global_opt.py:296-300):
+ * Xs [num_frames, H*W, 3] f32 -> Xs_out (may alias Xs) = z * ((u - cx)/fx, (v - cy)/fy, 1) with
+ * (u, v) the pixel of the point and Kmat [3,3] f32 on the device.  IEEE operations in the
+ * reference's order: bit-identical to the torch expression. */
+int frodo_constrain_points_to_ray(const float* Xs, const float* Kmat, int num_frames, int H, int W,
+                                  float* Xs_out, frodo_stream_t stream);
 int frodo_match_finish(const int64_t* p1, const void* scores, int scores_f16,
                        const uint8_t* valid_in, float threshold, int64_t* idx_1_to_2,
                        uint8_t* valid, int B, int N, int W, frodo_stream_t stream);

@@ -248,3 +248,28 @@ def test_sharded_driver_with_odometry_equals_single_call_bitwise(dev):
                     OP["sigma_odom_r"], OP["sigma_scale_prior"])
     db = sg.solve(3, 0.0)
     assert torch.equal(da, db) and torch.equal(Ta, Tb)
+
+
+def test_constrain_points_to_ray_bitwise(dev):
+    """geometry.py:37-42 as one kernel: bit-identical to the torch expression of the reference
+    evaluated on the GPU and to numpy float32 on the CPU; the arena applies it on put_keyframe."""
+    from frodo_slam_b200.graph import KeyframeGraphArena, constrain_points_to_ray
+    H, W = 37, 53
+    g = synth.keyframe_graph(3, H, W, [(0, 1), (1, 2)], seed=4, device=dev)
+    Xs, K = g["Xs"].contiguous(), g["K"].contiguous()
+    out = constrain_points_to_ray((H, W), Xs, K)
+    u, v = torch.meshgrid(torch.arange(W, device=dev), torch.arange(H, device=dev), indexing="xy")
+    uv = torch.stack((u, v), dim=-1).reshape(1, H * W, 2).float().repeat(3, 1, 1)
+    z = Xs[..., 2:3]
+    ref = torch.cat((z * ((uv[..., 0:1] - K[0, 2]) / K[0, 0]), z * ((uv[..., 1:2] - K[1, 2]) / K[1, 1]),
+                     z * 1.0), dim=-1)
+    assert torch.equal(out, ref)
+    Kn, Xn = K.cpu().numpy(), Xs.cpu().numpy()
+    un = (np.arange(H * W) % W).astype(np.float32)
+    vn = (np.arange(H * W) // W).astype(np.float32)
+    refn = np.stack([Xn[..., 2] * ((un - Kn[0, 2]) / Kn[0, 0]), Xn[..., 2] * ((vn - Kn[1, 2]) / Kn[1, 1]),
+                     Xn[..., 2]], axis=-1)
+    assert np.array_equal(out.cpu().numpy(), refn)
+    A = KeyframeGraphArena(H * W, 3, 2, device=dev)
+    A.put_keyframe(0, Xs[0], g["Cs"][0], g["Twc"][0], calib=((H, W), K))
+    assert torch.equal(A.Xs[0], ref[0])
