@@ -216,7 +216,13 @@ def run_matching(device, B, steps, warmup, peak, be=None, hw=None):
         "iter_proj": {"px_per_s": px / (ms_ip * 1e-3),
                       "roofline_frac": 65 * px / (ms_ip * 1e-3) / 1e9 / peak},
         "refine_matches": {"px_per_s": px / (ms_rm * 1e-3),
-                           "roofline_frac": 130 * px / (ms_rm * 1e-3) / 1e9 / peak},
+                           "roofline_frac": 130 * px / (ms_rm * 1e-3) / 1e9 / peak,
+                           # what actually bounds it: 5,880 packed-half
+                           # instructions per pixel at one per 2 cycles per SM sub-partition
+                           "bound": "packed-half pipe + shared-memory bandwidth",
+                           "pipe_floor_px_per_s": 148 * 4 * 1.965e9 / 2 * 32 / 5880,
+                           "frac_of_pipe_floor": px / (ms_rm * 1e-3) /
+                                                 (148 * 4 * 1.965e9 / 2 * 32 / 5880)},
         "roofline": {"bound": "hbm", "achieved": MATCH_BYTES_PER_PX * val / 1e9, "peak": peak,
                      "unit": "GB/s", "frac": MATCH_BYTES_PER_PX * val / 1e9 / peak,
                      "traffic": None},
