@@ -712,6 +712,16 @@ __device__ __forceinline__ void calib_pair(const RaysConst& c, float2 (&S)[28], 
   }
 }
 
+#ifdef FRODO_ACC_STAMPS
+__device__ unsigned long long g_acc_stamps[4 * 16384];
+__device__ int g_acc_shift = 0;
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t;
+}
+__device__ __forceinline__ unsigned smid() {
+  unsigned r; asm volatile("mov.u32 %0, %%smid;" : "=r"(r)); return r;
+}
+#endif
 template <int MODE>
 __global__ void __launch_bounds__(kRaysThreads, kRaysCtasPerSM)
 gn_accumulate_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
@@ -732,10 +742,20 @@ gn_accumulate_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
   extern __shared__ __align__(128) unsigned char stage_raw[];
   __shared__ __align__(8) uint64_t full_bar[kStages];
   __shared__ __align__(8) uint64_t empty_bar[kStages];
+#ifdef FRODO_ACC_STAMPS
+  const int lin0 = blockIdx.y * gridDim.x + blockIdx.x;
+  const int cta_lin = (lin0 + g_acc_shift) % (gridDim.x * gridDim.y);  // work item of this CTA
+  const int e = cta_lin / gridDim.x;
+  const int chunk = cta_lin % gridDim.x;
+#else
   const int e = blockIdx.y;
   const int chunk = blockIdx.x;
+#endif
   const int nchunks = gridDim.x;
   const int tid = threadIdx.x;
+#ifdef FRODO_ACC_STAMPS
+  if (tid == 32 && cta_lin < 16384) { g_acc_stamps[4 * cta_lin] = gtime(); g_acc_stamps[4 * cta_lin + 3] = smid(); }
+#endif
   const int ix = ii_row[e], jx = jj_row[e];
   const int k_begin = chunk * pts_per_cta;
   const int k_end = min(N, k_begin + pts_per_cta);
@@ -749,7 +769,11 @@ gn_accumulate_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
 
   // producer: one thread arms the stage barrier and issues the four bulk copies of tile t
   auto issue_tile = [&](int t) {
+#if FRODO_ABL == 6
+    const int k0 = k_begin + (t % kStages) * kTilePts;
+#else
     const int k0 = k_begin + t * kTilePts;
+#endif
     const uint32_t np = (uint32_t)min(kTilePts, k_end - k0);
     unsigned char* st = stage_raw + (size_t)(t % kStages) * kStageBytes;
     uint64_t* bar = &full_bar[t % kStages];
@@ -827,17 +851,35 @@ gn_accumulate_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
       const unsigned char* st = stage_raw + sg * kStageBytes;
       const long long* ip = reinterpret_cast<const long long*>(st + kOffIdx);
       const uint32_t dst = sm_gath + (uint32_t)gg * kGatherBytes;
-      long long ia = ip[tid];
-      if (st[kOffVm + tid] == 0) ia = 0;  // gn_kernels.cu:677
-      ptx::cp_async_16(dst, XCi + ia);
-      if (tid + kRaysThreads < left) {
-        long long ib = ip[tid + kRaysThreads];
-        if (st[kOffVm + tid + kRaysThreads] == 0) ib = 0;
-        ptx::cp_async_16(dst + 16u, XCi + ib);
+      // An unmatched point has weight zero whatever frame-i point stands beside it: the reference
+      // reads point 0 there (gn_kernels.cu:677); here nothing is loaded and the slot keeps what
+      // it held (the constant written below, or an earlier matched point: finite either way).
+      // Every CTA of keyframe i fetching the same 16 bytes is a hot spot in one L2 slice.
+      if (st[kOffVm + tid] != 0) {
+#if FRODO_ABL == 5
+        ptx::cp_async_16(dst, XCi + (k_end - left + tid));
+#else
+        ptx::cp_async_16(dst, XCi + ip[tid]);
+#endif
+      }
+      if (tid + kRaysThreads < left && st[kOffVm + tid + kRaysThreads] != 0) {
+#if FRODO_ABL == 5
+        ptx::cp_async_16(dst + 16u, XCi + (k_end - left + tid + kRaysThreads));
+#else
+        ptx::cp_async_16(dst + 16u, XCi + ip[tid + kRaysThreads]);
+#endif
       }
     }
   };
 
+  {  // this thread's slots of every gather buffer: a finite stand-in for unmatched points
+    float4* slot = reinterpret_cast<float4*>(stage_raw + kStages * kStageBytes) + 2 * tid;
+#pragma unroll
+    for (int g = 0; g <= kGatherDepth; ++g) {
+      slot[g * (kGatherBytes / 16)] = make_float4(1.f, 1.f, 1.f, 0.f);
+      slot[g * (kGatherBytes / 16) + 1] = make_float4(1.f, 1.f, 1.f, 0.f);
+    }
+  }
 #if FRODO_ABL != 4
 #pragma unroll
   for (int g = 0; g < kGatherDepth; ++g) {
@@ -914,27 +956,44 @@ gn_accumulate_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
   for (int k = 0; k < 28; ++k) S[k] = S2[k].x + S2[k].y;
 #pragma unroll
   for (int k = 0; k < 7; ++k) v[k] = v2[k].x + v2[k].y;
+#ifdef FRODO_ACC_STAMPS
+  if (tid == 32 && cta_lin < 16384) g_acc_stamps[4 * cta_lin + 1] = gtime();
+#endif
   edge_epilogue<kRaysThreads>(S, v, Ti, e, chunk, nchunks, nchunks, partials, tickets,
                               edge_blocks, peer);
+#ifdef FRODO_ACC_STAMPS
+  if (tid == 32 && cta_lin < 16384) g_acc_stamps[4 * cta_lin + 2] = gtime();
+#endif
 }
 
 
 }  // namespace
 
-// Points per accumulate CTA: minimises ceil(waves) * (points + fixed per-CTA cost) over a few
-// multiples of the 512-point tile (2 CTAs per SM; the fixed cost ~ 1500 points covers the
-// pipeline fill and the reduction epilogue).
+// Points per accumulate CTA, from a model of how the grid fills the device: `full` rounds in
+// which every SM holds kRaysCtasPerSM CTAs, then a last round with r = 1..4 CTAs per SM, where a
+// CTA sharing its SM with fewer neighbours runs faster (g(r), measured: a 3-CTA SM finishes in
+// 0.8 of the time of a 4-CTA one, 2 CTAs in 0.645, 1 in 0.53).  Each CTA costs its points plus
+// ~400 points of pipeline fill and reduction epilogue.  Fitted to the sweep in
+// profiles/r2_points_per_cta.txt (E = 24 ... 256 at 512x384); picks within 2 % of the best there.
 int gn_pts_per_cta(int E, int N) {
-  const long long cand[] = {2048, 4096, 6144, 8192, 12288, 16384, 24576, 32768};
-  const double slots = (double)kRaysCtasPerSM * num_sms();
+  static const int forced = [] {  // development override
+    const char* e = getenv("FRODO_GN_PPC");
+    return e ? atoi(e) : 0;
+  }();
+  if (forced > 0) return forced;
+  static_assert(kRaysCtasPerSM == 4, "g() below is measured for four CTAs per SM");
+  const double g[5] = {0.0, 0.53, 0.645, 0.8, 1.0};
+  const long long cand[] = {2048, 3072, 4096, 6144, 8192, 12288, 16384, 24576, 32768};
+  const long long sms = num_sms(), slots = (long long)kRaysCtasPerSM * sms;
   long long best = 2048;
   double best_cost = 1e300;
   for (long long ppc : cand) {
     const long long nch = ((long long)(N > 0 ? N : 1) + ppc - 1) / ppc;
-    const double waves = (double)(nch * (long long)(E > 0 ? E : 1)) / slots;
-    const double rounds = waves <= 1.0 ? 1.0 : (double)(long long)(waves + 0.999999);
+    const long long ncta = nch * (long long)(E > 0 ? E : 1);
+    const long long full = ncta / slots, rem = ncta - full * slots;
+    const long long r = (rem + sms - 1) / sms;  // CTAs per SM in the last round
     const long long eff = ppc < N ? ppc : ((N + kTilePts - 1) / kTilePts) * kTilePts;
-    const double cost = rounds * ((double)eff + 1500.0);
+    const double cost = ((double)eff + 400.0) * ((double)full + g[r]);
     if (cost < best_cost) {
       best_cost = cost;
       best = ppc;
@@ -943,6 +1002,14 @@ int gn_pts_per_cta(int E, int N) {
   return (int)best;
 }
 
+#ifdef FRODO_ACC_STAMPS
+extern "C" int frodo_debug_acc_shift(int shift) {
+  return (int)cudaMemcpyToSymbol(g_acc_shift, &shift, sizeof(int));
+}
+extern "C" int frodo_debug_acc_stamps(unsigned long long* host, int n) {
+  return (int)cudaMemcpyFromSymbol(host, g_acc_stamps, (size_t)n * 4 * 8);
+}
+#endif
 size_t gn_packed_bytes(int K, int N) {
   const size_t k = (size_t)(K > 0 ? K : 1), n = (size_t)(N > 0 ? N : 1);
   const size_t nb = (n + kTilePts - 1) / kTilePts;

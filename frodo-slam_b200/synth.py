@@ -178,6 +178,9 @@ def graph_edges(cfg, seed=2):
         else:
             K, n_loop, min_gap = (64, 65, 8) if cfg == "loop64" else (32, 33, 4)
         und = [(k - 1, k) for k in range(1, K)]
+        available = sum(K - g for g in range(min_gap, K))  # pairs (i, j) with j - i >= min_gap
+        if n_loop > available:
+            raise ValueError(f"{cfg}: {n_loop} loop closures asked, {available} distinct pairs exist")
         gen = torch.Generator().manual_seed(seed)
         seen = set(und)
         while len(und) < K - 1 + n_loop:
