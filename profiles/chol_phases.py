@@ -18,6 +18,9 @@ import torch  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--kf", default="loop64")
 ap.add_argument("--hw", default="96x128")
+ap.add_argument("--insitu", action="store_true",
+                help="stamps of the LAST iteration of a whole 10-iteration frodo_gauss_newton call "
+                     "(tiles built from the per-edge blocks, caches as the accumulate leaves them)")
 args = ap.parse_args()
 H, W = (int(x) for x in args.hw.split("x"))
 
@@ -61,7 +64,20 @@ def solve():
 
 
 times = []
-for it in range(6):
+if args.insitu:
+    for rep in range(3):
+        Twc.copy_(g["Twc"])
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.check(lib.frodo_gauss_newton(
+            ctypes.byref(prm), _ptr(Twc), _ptr(g["Xs"]), _ptr(g["Cs"]), None, _ptr(g["ii"]),
+            _ptr(g["jj"]), _ptr(g["idx_ii2jj"]), _ptr(g["valid_match"]), _ptr(g["Q"]), K, N, E, 1,
+            10, 0.0, _ptr(dx), None, _ptr(ws), nbytes, s))
+        e1.record()
+        torch.cuda.synchronize()
+        times.append(e0.elapsed_time(e1) * 1e3 / 10)
+    print("IN SITU: whole call / 10 iterations (us per iteration) follows as 'kernel' times")
+for it in range(0 if args.insitu else 6):
     Twc.copy_(g["Twc"])
     system()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -74,7 +90,8 @@ st = ws[st_off:st_off + 1024 * 8].view(torch.int64).cpu().numpy().astype("float6
 mhz = 1965.0
 us = lambda a, b: (b - a) / mhz  # noqa: E731
 print(f"n={n} T={T} Tc={Tc}; kernel by CUDA events (us): " + " ".join(f"{t:.1f}" for t in times))
-print(f"(clock64 cycles of the spine CTA at {mhz:.0f} MHz -> us; dense-Hg tile build)")
+print(f"(clock64 cycles of the spine CTA at {mhz:.0f} MHz -> us; "
+      + ("tiles from per-edge blocks, in situ)" if args.insitu else "dense-Hg tile build)"))
 print(f"wait for + load the first diagonal tile {us(st[0], st[1]):8.2f} us")
 tot = {"factor+invert": 0.0, "panel+publish": 0.0, "diag update": 0.0}
 for k in range(Tc):
