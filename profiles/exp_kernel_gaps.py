@@ -6,6 +6,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
 from torch.profiler import profile, ProfilerActivity
+from frodo_slam_b200 import _lib
+if os.environ.get("ALTLIB"):
+    _lib.LIB_PATH = os.path.join(ROOT, os.environ["ALTLIB"])
 from frodo_slam_b200 import backends, synth
 dev = torch.device("cuda:0")
 H, W = 384, 512
