@@ -50,7 +50,7 @@ size_t gn_carve_workspace(void* base, int K, int E, int N, GnWorkspace* ws) {
   const size_t o_hg = take((n + 1) * n * sizeof(double));
   const size_t o_ii = take(Ez * sizeof(int32_t));
   const size_t o_jj = take(Ez * sizeof(int32_t));
-  const size_t o_sc = take(8 * sizeof(int32_t));
+  const size_t o_sc = take((8 + (size_t)(K > 0 ? K : 1)) * sizeof(int32_t));
   const size_t o_tk = take(Ez * sizeof(int32_t));
   const size_t o_pt = take(Ez * max_chunks * kGnBlock * sizeof(float));
   const size_t o_eb = take(Ez * kGnBlock * sizeof(double));
@@ -63,6 +63,7 @@ size_t gn_carve_workspace(void* base, int K, int E, int N, GnWorkspace* ws) {
     ws->ii_row = reinterpret_cast<int32_t*>(b + o_ii);
     ws->jj_row = reinterpret_cast<int32_t*>(b + o_jj);
     ws->scalars = reinterpret_cast<int32_t*>(b + o_sc);
+    ws->kf_need = ws->scalars + 8;
     ws->tickets = reinterpret_cast<int32_t*>(b + o_tk);
     ws->partials = reinterpret_cast<float*>(b + o_pt);
     ws->edge_blocks = reinterpret_cast<double*>(b + o_eb);
@@ -585,7 +586,13 @@ int frodo_gauss_newton_sharded(const frodo_gn_params* params, float* Twc, const 
   if (rc) return rc;
   const float* XC = nullptr;
   if (El > 0 && N > 0 && (N % 16) == 0 && max_iter > 0) {
-    rc = launch_gn_pack_points(Xs, Cs, K, N, ws.packed, s);
+    const int32_t* need = nullptr;
+    if (El < E) {  // a slice of the edges reads only some of the pointmaps
+      rc = launch_gn_mark_keyframes(ii_row + edge_lo, jj_row + edge_lo, El, K, ws.kf_need, s);
+      if (rc) return rc;
+      need = ws.kf_need;
+    }
+    rc = launch_gn_pack_points(Xs, Cs, K, N, ws.packed, s, need);
     if (rc) return rc;
     XC = ws.packed;
   }

@@ -523,7 +523,7 @@ constexpr int kRaysSmemBytes = kStages * kStageBytes + (kGatherDepth + 1) * kGat
 // pair slot (keyframe f, block b, pair p): points n = 512 b + p and n + 256.
 __global__ void pack_points_kernel(const float* __restrict__ Xs, const float* __restrict__ Cs,
                                    float4* __restrict__ XC, float4* __restrict__ XP, int K, int N,
-                                   int NB) {
+                                   int NB, const int32_t* __restrict__ need) {
   const size_t slots = (size_t)K * NB * kRaysThreads;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < slots; k += stride) {
@@ -531,20 +531,37 @@ __global__ void pack_points_kernel(const float* __restrict__ Xs, const float* __
     const size_t fb = k / kRaysThreads;
     const int b = (int)(fb % NB);
     const size_t f = fb / NB;
+    const int want = need != nullptr ? __ldg(need + f) : 3;  // 1: XC row read, 2: XP row read
+    if (want == 0) continue;
     const int nA = b * kTilePts + p, nB = nA + kRaysThreads;
     float4 A = make_float4(0.f, 0.f, 0.f, 0.f), Bv = A;
     if (nA < N) {
       const float* x = Xs + (f * N + nA) * 3;
       A = make_float4(__ldg(x), __ldg(x + 1), __ldg(x + 2), __ldg(Cs + f * N + nA));
-      XC[f * N + nA] = A;
+      if (want & 1) XC[f * N + nA] = A;
     }
     if (nB < N) {
       const float* x = Xs + (f * N + nB) * 3;
       Bv = make_float4(__ldg(x), __ldg(x + 1), __ldg(x + 2), __ldg(Cs + f * N + nB));
-      XC[f * N + nB] = Bv;
+      if (want & 1) XC[f * N + nB] = Bv;
     }
-    XP[2 * k] = make_float4(A.x, Bv.x, A.y, Bv.y);
-    XP[2 * k + 1] = make_float4(A.z, Bv.z, A.w, Bv.w);
+    if (want & 2) {
+      XP[2 * k] = make_float4(A.x, Bv.x, A.y, Bv.y);
+      XP[2 * k + 1] = make_float4(A.z, Bv.z, A.w, Bv.w);
+    }
+  }
+}
+
+// need[k] |= 1 if keyframe row k is the i of one of the E edges, |= 2 if it is the j.  One CTA.
+__global__ void mark_keyframes_kernel(const int32_t* __restrict__ ii_row,
+                                      const int32_t* __restrict__ jj_row, int E, int K,
+                                      int32_t* __restrict__ need) {
+  for (int k = threadIdx.x; k < K; k += blockDim.x) need[k] = 0;
+  __syncthreads();
+  for (int e = threadIdx.x; e < E; e += blockDim.x) {
+    const int i = ii_row[e], j = jj_row[e];
+    if (i >= 0 && i < K) atomicOr(need + i, 1);
+    if (j >= 0 && j < K) atomicOr(need + j, 2);
   }
 }
 
@@ -1016,8 +1033,16 @@ size_t gn_packed_bytes(int K, int N) {
   return k * n * 16 + k * nb * kTilePts * 16;  // XC, then XP padded to whole blocks
 }
 
+int launch_gn_mark_keyframes(const int32_t* ii_row, const int32_t* jj_row, int E, int K,
+                             int32_t* need, cudaStream_t s) {
+  if (K <= 0) return FRODO_OK;
+  mark_keyframes_kernel<<<1, 256, 0, s>>>(ii_row, jj_row, E, K, need);
+  FRODO_CUDA_TRY(cudaGetLastError());
+  return FRODO_OK;
+}
+
 int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float* XC,
-                          cudaStream_t s) {
+                          cudaStream_t s, const int32_t* need) {
   const size_t total = (size_t)K * (size_t)N;
   if (total == 0) return FRODO_OK;
   const int NB = (N + kTilePts - 1) / kTilePts;
@@ -1026,7 +1051,7 @@ int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float*
   const size_t resident = (size_t)8 * (size_t)num_sms();
   const int blocks = (int)(want < resident ? want : resident);
   float4* xc = reinterpret_cast<float4*>(XC);
-  pack_points_kernel<<<blocks, 256, 0, s>>>(Xs, Cs, xc, xc + total, K, N, NB);
+  pack_points_kernel<<<blocks, 256, 0, s>>>(Xs, Cs, xc, xc + total, K, N, NB, need);
   FRODO_CUDA_TRY(cudaGetLastError());
   return FRODO_OK;
 }
@@ -1040,7 +1065,7 @@ int launch_gn_pack_slot(const float* X, const float* C, int K_total, int slot, i
   float4* xc = reinterpret_cast<float4*>(XC);
   float4* xc_row = xc + (size_t)slot * N;
   float4* xp_row = xc + (size_t)K_total * N + (size_t)slot * NB * kRaysThreads * 2;
-  pack_points_kernel<<<blocks, 256, 0, s>>>(X, C, xc_row, xp_row, 1, N, NB);
+  pack_points_kernel<<<blocks, 256, 0, s>>>(X, C, xc_row, xp_row, 1, N, NB, nullptr);
   FRODO_CUDA_TRY(cudaGetLastError());
   return FRODO_OK;
 }

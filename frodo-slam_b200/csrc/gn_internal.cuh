@@ -13,6 +13,7 @@ struct GnWorkspace {
   int32_t* ii_row;     // [E]
   int32_t* jj_row;     // [E]
   int32_t* scalars;    // [8]: 0 n_unique, 1 done, 2..3 info
+  int32_t* kf_need;    // [K]: launch_gn_mark_keyframes (edge-sharded solves)
   int32_t* tickets;    // [E]  (zero between launches)
   float* partials;     // [E * nchunks * 35]
   double* edge_blocks; // [E * 35]
@@ -50,8 +51,13 @@ int launch_gn_add_odom(const GnOdom& od, const float* Twc, int K, int num_fix, d
                        const int32_t* done, void* scratch, cudaStream_t s);
 // Bytes of the packed pointmap region (XC [K][N] float4 + XP padded to 512-point blocks).
 size_t gn_packed_bytes(int K, int N);
+// `need` (may be null): per keyframe, bit 0 = its XC row is read (it is the i of an edge of this
+// rank), bit 1 = its XP row is (it is the j); rows nobody reads are not packed.
 int launch_gn_pack_points(const float* Xs, const float* Cs, int K, int N, float* XC,
-                          cudaStream_t s);
+                          cudaStream_t s, const int32_t* need = nullptr);
+// need[k] for the keyframe rows 0..K-1 from the edges [0, E) of ii_row / jj_row.
+int launch_gn_mark_keyframes(const int32_t* ii_row, const int32_t* jj_row, int E, int K,
+                             int32_t* need, cudaStream_t s);
 // One keyframe (X [N,3], C [N]) into row `slot` of a packed region laid out for K_total keyframes.
 int launch_gn_pack_slot(const float* X, const float* C, int K_total, int slot, int N, float* XC,
                         cudaStream_t s);
