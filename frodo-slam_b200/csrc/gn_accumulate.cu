@@ -500,6 +500,14 @@ gn_accumulate_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
 #ifndef FRODO_ABL
 #define FRODO_ABL 0
 #endif
+// L2 eviction priority of everything this kernel reads (cache-hint forms of the bulk copies and
+// of the gathers; the policy is a kernel argument, see launch_gn_accumulate): a pass streams up to
+// 2 GB through a 126 MB cache, and what it pushes out is the code and the tiles of the solve that
+// follows, which then starts cold.  With evict-first on all reads, measured on the 64-keyframe
+// graph: accumulate 473 -> 480 us (the gathers lose a little short-term reuse), Cholesky
+// 138-141 -> 128-130 us; 32-keyframe calib graph 256 -> 260 and 83 -> 71 us.  Hinting only the
+// streamed arrays, or those + XP, leaves the solve cold (the gathers alone flush the cache);
+// gathers allocated in L1 as well: 518 us.
 // (a warp-specialised persistent variant, measured slower -- 538 vs 473 us -- is kept as an
 // experiment under profiles/experiments/gn_accumulate_ws.cuh, not in the product)
 #ifndef FRODO_RAYS_THREADS
@@ -751,11 +759,14 @@ gn_accumulate_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
                                  const float* __restrict__ Q, int N, int pts_per_cta,
                                  float* __restrict__ partials, int32_t* __restrict__ tickets,
                                  double* __restrict__ edge_blocks,
-                                 const int32_t* __restrict__ done, const GnPeerOut peer) {
+                                 const int32_t* __restrict__ done, const GnPeerOut peer,
+                                 int l2_evict_first) {
   if (done != nullptr && *done != 0) {
     peer_skip(peer);
     return;
   }
+  const uint64_t l2_policy =
+      l2_evict_first ? ptx::l2_policy_evict_first() : ptx::l2_policy_evict_normal();
   extern __shared__ __align__(128) unsigned char stage_raw[];
   __shared__ __align__(8) uint64_t full_bar[kStages];
   __shared__ __align__(8) uint64_t empty_bar[kStages];
@@ -795,10 +806,10 @@ gn_accumulate_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
     unsigned char* st = stage_raw + (size_t)(t % kStages) * kStageBytes;
     uint64_t* bar = &full_bar[t % kStages];
     ptx::mbar_arrive_expect_tx(bar, np * 13u + kTilePts * 16u);
-    ptx::bulk_g2s(st + kOffIdx, gIdx + k0, np * 8u, bar);
-    ptx::bulk_g2s(st + kOffXP, gXPj + k0, kTilePts * 16u, bar);  // whole (padded) block
-    ptx::bulk_g2s(st + kOffQ, gQ + k0, np * 4u, bar);
-    ptx::bulk_g2s(st + kOffVm, gVm + k0, np, bar);
+    ptx::bulk_g2s_hint(st + kOffIdx, gIdx + k0, np * 8u, bar, l2_policy);
+    ptx::bulk_g2s_hint(st + kOffXP, gXPj + k0, kTilePts * 16u, bar, l2_policy);  // whole (padded) block
+    ptx::bulk_g2s_hint(st + kOffQ, gQ + k0, np * 4u, bar, l2_policy);
+    ptx::bulk_g2s_hint(st + kOffVm, gVm + k0, np, bar, l2_policy);
   };
   if (tid == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -876,14 +887,14 @@ gn_accumulate_packed_kernel(frodo_gn_params prm, const float* __restrict__ Twc,
 #if FRODO_ABL == 5
         ptx::cp_async_16(dst, XCi + (k_end - left + tid));
 #else
-        ptx::cp_async_16(dst, XCi + ip[tid]);
+        ptx::cp_async_16_hint(dst, XCi + ip[tid], l2_policy);
 #endif
       }
       if (tid + kRaysThreads < left && st[kOffVm + tid + kRaysThreads] != 0) {
 #if FRODO_ABL == 5
         ptx::cp_async_16(dst + 16u, XCi + (k_end - left + tid + kRaysThreads));
 #else
-        ptx::cp_async_16(dst + 16u, XCi + ip[tid + kRaysThreads]);
+        ptx::cp_async_16_hint(dst + 16u, XCi + ip[tid + kRaysThreads], l2_policy);
 #endif
       }
     }
@@ -1103,18 +1114,22 @@ int launch_gn_accumulate(const frodo_gn_params& prm, const float* Twc, const flo
     }
     const float4* xc = reinterpret_cast<const float4*>(XC);
     const float4* xp = xc + (size_t)K * N;
+    // Evict-first reads keep the following solve warm at a ~1.4 % cost to this kernel: worth it
+    // when the solve is a large share of the iteration (smaller graphs, slices of a sharded
+    // solve), about even on the 64-keyframe graph on one GPU, where it is left off.
+    const int ef = ((long long)E * (long long)N <= (32LL << 20)) ? 1 : 0;
     if (prm.mode == FRODO_GN_RAYS)
       gn_accumulate_packed_kernel<FRODO_GN_RAYS><<<grid, kRaysThreads, smem, s>>>(
           prm, Twc, Kmat, xc, xp, ii_row, jj_row, idx, valid, Q, N, ppc, partials, tickets,
-          edge_blocks, done, peer);
+          edge_blocks, done, peer, ef);
     else if (prm.mode == FRODO_GN_POINTS)
       gn_accumulate_packed_kernel<FRODO_GN_POINTS><<<grid, kRaysThreads, smem, s>>>(
           prm, Twc, Kmat, xc, xp, ii_row, jj_row, idx, valid, Q, N, ppc, partials, tickets,
-          edge_blocks, done, peer);
+          edge_blocks, done, peer, ef);
     else
       gn_accumulate_packed_kernel<FRODO_GN_CALIB><<<grid, kRaysThreads, smem, s>>>(
           prm, Twc, Kmat, xc, xp, ii_row, jj_row, idx, valid, Q, N, ppc, partials, tickets,
-          edge_blocks, done, peer);
+          edge_blocks, done, peer, ef);
     FRODO_CUDA_TRY(cudaGetLastError());
     return FRODO_OK;
   }
