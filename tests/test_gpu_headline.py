@@ -225,3 +225,38 @@ def test_refine_matches_224_vs_oracle(be, dev):
                                    MP["dilation_max"])
     assert np.array_equal(pn.cpu().numpy(), pr)
     assert np.array_equal(sc.cpu().numpy().view(np.uint16), sr.view(np.uint16))
+
+
+# ------------------------------------------------ an edge slice alone (masked pointmap pack)
+
+def test_edge_slice_alone_equals_subgraph_bitwise(dev):
+    """frodo_gauss_newton_sharded on ONE rank with a strict slice of the edges and no peers: the
+    blocks of the other edges are zero (workspace zeroed here), so the solve is the one of the
+    sub-graph made of the slice.  A slice packs only the pointmaps it reads (keyframe 0 is never
+    a j, the last one never an i in the chain half): same poses, bit for bit, as the operator
+    on the sub-graph."""
+    from frodo_slam_b200 import backends, dist as fdist
+    g = synth.keyframe_graph(*_sized("loop64", 96, 128), seed=3, device=dev)
+    E, N = g["ii"].shape[0], g["Xs"].shape[1]
+    lo, hi = 0, E // 2  # the undirected edges in their forward direction: all 64 keyframes appear
+    assert torch.unique(torch.cat([g["ii"][lo:hi], g["jj"][lo:hi]])).numel() == g["Xs"].shape[0]
+    prm = backends.make_params("rays", sigma_ray=GP["sigma_ray"], sigma_dist=GP["sigma_dist"],
+                               C_thresh=GP["C_conf"], Q_thresh=GP["Q_conf"])
+    idx, valid, Q = (g[k].view(E, N)[lo:hi].contiguous() for k in ("idx_ii2jj", "valid_match", "Q"))
+    T_slice = g["Twc"].clone()
+    sg = fdist.ShardedGaussNewton(prm, T_slice, g["Xs"], g["Cs"], None, g["ii"], g["jj"], idx, valid,
+                                  Q, lo, hi, 1)
+    sg.ws_all = torch.zeros(sg.nbytes_all, dtype=torch.uint8, device=dev)
+    sg._solve_one_call(4, 0.0)
+    T_sub = g["Twc"].clone()
+    backends.gauss_newton_rays(T_sub, g["Xs"], g["Cs"], g["ii"][lo:hi].contiguous(),
+                               g["jj"][lo:hi].contiguous(), idx, valid, Q, GP["sigma_ray"],
+                               GP["sigma_dist"], GP["C_conf"], GP["Q_conf"], 1, 4, 0.0)
+    torch.cuda.synchronize()
+    assert float((T_sub - g["Twc"]).abs().max()) > 1e-4  # the poses moved
+    assert torch.equal(T_slice, T_sub)
+
+
+def _sized(cfg, H, W):
+    K, und = synth.graph_edges(cfg)
+    return K, H, W, und
