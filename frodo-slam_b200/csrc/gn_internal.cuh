@@ -111,6 +111,10 @@ int launch_chol_flow(const double* Hg, const double* edge_blocks, const int32_t*
                      int n_max, int* handled, cudaStream_t s, const int32_t* pose_rows = nullptr,
                      const uint32_t* wait_counter = nullptr, uint32_t wait_target = 0);
 // Spins (one thread, bounded) until *counter has reached target; on time-out bumps info[1].
+int launch_chol_small(const double* edge_blocks, const int32_t* ii_row, const int32_t* jj_row,
+                      int E, float* Twc, float* dx, int K, int num_fix, float delta_thresh,
+                      int32_t* done, int32_t* info, int* handled, cudaStream_t s,
+                      const int32_t* pose_rows);
 int launch_gn_peer_wait(const uint32_t* counter, uint32_t target, const int32_t* done,
                         int32_t* info, cudaStream_t s);
 

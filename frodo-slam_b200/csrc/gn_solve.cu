@@ -300,6 +300,16 @@ int launch_gn_solve_retract(const GnSystem& sys, float* Twc, float* dx, int K, i
                               s);
   };
   if (n <= kSmallN) {  // sliding-window sized systems: one CTA, system in shared memory
+    if (!sys.dense) {  // straight from the per-edge blocks (gn_chol_flow.cu, chol_small_kernel)
+      if (sys.wait_counter != nullptr) {
+        const int wrc = launch_gn_peer_wait(sys.wait_counter, sys.wait_target, done, info, s);
+        if (wrc != FRODO_OK) return wrc;
+      }
+      int handled = 0;
+      const int src = launch_chol_small(sys.edge_blocks, sys.ii_row, sys.jj_row, sys.E, Twc, dx, K,
+                                        num_fix, delta_thresh, done, info, &handled, s, pose_rows);
+      if (src != FRODO_OK || handled) return src;
+    }
     const int rc = need_dense();
     if (rc != FRODO_OK) return rc;
     solve_small_kernel<<<1, kSmallThreads, 0, s>>>(Hg, Twc, dx, n, K, num_fix, delta_thresh, done,

@@ -11,7 +11,7 @@ if os.environ.get("ALTLIB"):
     _lib.LIB_PATH = os.path.join(ROOT, os.environ["ALTLIB"])
 from frodo_slam_b200 import backends, synth
 dev = torch.device("cuda:0")
-H, W = 384, 512
+H, W = (int(x) for x in os.environ.get("HW", "384x512").split("x"))
 gp = synth.GN_PARAMS
 for cfg in os.environ.get("CFGS", "window8,loop64").split(","):
     K, und = synth.graph_edges(cfg)
